@@ -1,0 +1,173 @@
+/*
+ * umetrack_b200 -- C ABI of the B200 (sm_100a) implementation of UmeTrack's per-frame
+ * multi-view inference path.
+ *
+ * The reference (facebookresearch/UmeTrack) is pure Python and has no native / FFI boundary;
+ * its drop-in surface is the Python API in lib/tracker and lib/models.  This library sits
+ * underneath the Python mirror of that API (package `umetrack_b200`), which binds it with
+ * ctypes.  Each entry point below cites the reference function(s) it replaces
+ * (file:line relative to the reference checkout).
+ *
+ * Conventions
+ *   - every function returns 0 on success and a non-zero code on failure; the message is
+ *     available from umt_last_error() (thread-local);
+ *   - unless a parameter says "host", pointers are DEVICE pointers owned by the caller;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream);
+ *   - no function synchronises the device; nothing is copied to the host;
+ *   - except umt_model_create / umt_model_destroy, no function allocates memory.
+ */
+#ifndef UMETRACK_B200_H
+#define UMETRACK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UMT_OK 0
+#define UMT_ERR_INVALID 1
+#define UMT_ERR_CUDA 2
+#define UMT_ERR_UNSUPPORTED 3
+
+#define UMT_CROP 96            /* crop edge length (lib/models/model_loader.py:56) */
+#define UMT_RESAMPLE_PARAMS 48 /* doubles per crop for umt_resample_crops */
+#define UMT_N_JOINTS 22
+#define UMT_N_LANDMARKS 21
+
+/* numeric mode of the encoder convolutions */
+#define UMT_MODE_FP32_EQUIV 0 /* split-bf16 (hi+lo) operands, 3 tensor-core products, fp32 accumulate */
+#define UMT_MODE_BF16 1       /* single bf16 product, fp32 accumulate */
+
+/* regression head */
+#define UMT_HEAD_KNOWN_SKELETON 0   /* _regressor_k, regress_pose_use_skeleton */
+#define UMT_HEAD_UNKNOWN_SKELETON 1 /* _regressor_u, regress_pose_pred_skel_scale */
+
+const char* umt_last_error(void);
+int umt_abi_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Stage (a): fisheye -> pinhole crop resampling.
+ * Replaces `_warp_image` (lib/tracker/tracker.py:54-80): the float64 camera chain
+ * window_to_eye / eye_to_world / world_to_eye / eye_to_window (lib/common/camera.py:257-281,
+ * 68-85, 120-141), the float32 cast of the map, and cv2.remap(uint8, INTER_LINEAR,
+ * BORDER_CONSTANT 0) in its 1/32-pixel fixed-point form; plus the `/255` conversion of
+ * `_make_inputs` (tracker.py:211).
+ *
+ * params[n_crops][48] (float64): src fx fy cx cy | k1 k2 k3 k4 p1 p2 k5 k6 |
+ *   src camera_to_world (16, row major, mm) | crop fx fy cx cy | crop camera_to_world (16).
+ * Source pixel (x,y) of crop i is src_base[src_offset[i] + y*src_pitch + x]; this expresses
+ * the reference's strided view frame[:, cam, :] of a [H, 4, W] frame.
+ * Any of out_u8 / out_f32 / out_idx may be NULL.  out_idx receives (ix, iy, fx, fy) per
+ * pixel: integer tap origin and 5-bit fractions, the quantities that must be bit-exact.
+ */
+int umt_resample_crops(const uint8_t* src_base, const int64_t* src_offset, int src_pitch,
+                       int src_w, int src_h, const double* params, int n_crops,
+                       uint8_t* out_u8 /* [n,96,96] */, float* out_f32 /* [n,96,96] */,
+                       int32_t* out_idx /* [n,96,96,4] */, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Stage (b): per-view encoder, multi-view fusion, temporal memory, pose regression.
+ * Replaces UmeTrackModel.regress_pose_use_skeleton / regress_pose_pred_skel_scale
+ * (lib/models/umetrack_model.py:188-242) and everything they call: the ResNet backbone
+ * (backbone_resnet.py:14-158, model_utils.py:107-138), FTL + fusion
+ * (feature_extractor.py:61-141, model_utils.py:57-104,141-192), SimpleConvRNN
+ * (temporal.py:51-139), SkeletonEncoder (skeleton_encoder.py:28-53), PoseRegressor and its
+ * decoders (regressor.py:76-186, model_utils.py:17-54) and _recover_wrist_xfs_in_world
+ * (umetrack_model.py:77-90).
+ */
+typedef struct umt_model umt_model;
+
+/* Number / name / element count of the weight tensors umt_model_create expects, in order:
+ * the reference's flat state_dict (lib/models/model_loader.py:84-87) without the
+ * `num_batches_tracked` counters. */
+int umt_model_num_tensors(void);
+const char* umt_model_tensor_name(int i);
+int64_t umt_model_tensor_numel(int i);
+
+/* host_tensors: HOST pointers to float32 arrays, one per tensor above.  BatchNorm is folded,
+ * weights are split into bf16 hi/lo pairs, packed for the tensor-core kernels and uploaded to
+ * the current device (the only device allocations this library makes). */
+int umt_model_create(const float* const* host_tensors, int n_tensors, umt_model** out);
+void umt_model_destroy(umt_model* m);
+
+/* Scratch memory (encoder activations of one chunk of `chunk_images` crops, per-batch tail
+ * buffers).  The caller allocates `bytes` on the device (256-byte aligned) and binds it; binding
+ * clears it once (the kernels rely on zero halo positions inside it).  max_images / max_samples
+ * bound n_img / n_samples of later calls; batches larger than chunk_images run the encoder in
+ * several passes over the same scratch. */
+int umt_model_workspace_bytes(const umt_model* m, int chunk_images, int max_images,
+                              int max_samples, size_t* bytes);
+int umt_model_bind_workspace(umt_model* m, void* workspace, size_t bytes, int chunk_images,
+                             int max_images, int max_samples, void* stream);
+
+/* One forward pass over n_samples hand-frames built from n_img crops.
+ * Inputs as in InputFrameData / InputFrameDesc / InputSkeletonData
+ * (lib/models/umetrack_model.py:21-74): images [n_img,96,96] in [0,1]; intrinsics [n_img,3,3];
+ * extrinsics [n_img,4,4] (world -> crop eye, metres); sample_range [n_samples,2] (1 or 2
+ * views per sample); memory_idx, hand_idx [n_samples]; use_memory [n_samples] (bytes).
+ * skel_axes / skel_rest [n_skel,22,3] with n_skel in {1, n_samples} (known-skeleton head
+ * only).  mem_state [n_slots,18,6,6] and prev_extr [n_slots,4,4] are the recurrent state of
+ * SimpleConvRNN (temporal.py:41-42), updated in place.
+ * Outputs: joint_angles [n_samples,22]; wrist [n_samples,4,4] in world space (right hands
+ * un-mirrored); scale [n_samples] (unknown-skeleton head, else may be NULL); sigma
+ * [n_samples,21]. */
+int umt_model_forward(umt_model* m, int mode, int head, const float* images,
+                      const float* intrinsics, const float* extrinsics,
+                      const int64_t* sample_range, const int64_t* memory_idx,
+                      const uint8_t* use_memory, const int64_t* hand_idx, int n_img,
+                      int n_samples, const float* skel_axes, const float* skel_rest, int n_skel,
+                      float* mem_state, float* prev_extr, int n_slots, float* out_joint_angles,
+                      float* out_wrist, float* out_scale, float* out_sigma, void* stream);
+
+/* Backbone only: images [n_img,96,96] -> features [n_img,72,6,6]
+ * (`_image_backbone`, lib/models/model_utils.py:107-138).  Uses the bound workspace. */
+int umt_model_encode(umt_model* m, int mode, const float* images, int n_img, float* features,
+                     void* stream);
+
+/* Number of kernels the last umt_model_forward / umt_model_encode call launched. */
+int umt_model_last_launch_count(const umt_model* m);
+
+/* Measurement hook: one encoder pass over n_img crops (one chunk) with a CUDA event between
+ * consecutive launches; out_ms is a HOST float[32]: stem, the 30 convolutions in execution order,
+ * projection.  Synchronises the stream (this is the only entry point that does). */
+int umt_model_profile_layers(umt_model* m, int mode, const float* images, int n_img, float* out_ms,
+                             void* stream);
+
+/* Test hook: run the encoder on `images` [n_img,96,96] up to convolution `layer` (0..29,
+ * execution order), then evaluate that layer twice on the same inputs: with plain CUDA-core
+ * arithmetic into out_simt and with the tensor-core kernel into out_umma, both as dense float32
+ * [n_img, C, H, W] (no halo), so the tensor-core path can be checked layer by layer.  Either
+ * output may be NULL.  out_shape is a HOST int[3] receiving C, H, W. */
+int umt_model_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
+                          float* out_simt, float* out_umma, int* out_shape, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Stage (c): forward kinematics + skinning, and metric reductions.
+ * umt_fk_landmarks replaces skin_landmarks (lib/common/hand_skinning.py:17-209) including the
+ * right-hand column flip of landmarks_from_hand_pose (lib/tracker/perspective_crop.py:40-51).
+ * Hand model arrays are float32: axes/rest [22,3], lm_rest [21,3], lm_idx [21,3] (stored as
+ * float like the reference's torch.Tensor(list)), lm_w [21,3].  mirror [n] (bytes) may be
+ * NULL.  units follow the inputs (mm in the tracker).
+ */
+int umt_fk_landmarks(const float* axes, const float* rest, const float* lm_rest,
+                     const float* lm_idx, const float* lm_w, const float* joint_angles /* [n,22] */,
+                     const float* wrist /* [n,4,4] */, const uint8_t* mirror, int n,
+                     float* out /* [n,21,3] */, void* stream);
+
+/* sums[0] += sum over valid i of mean_21 |gt_i - pred_i|_2 ; sums[1] += number of valid i.
+ * (run_eval_known_skeleton.py:88-89,117-119).  pred/gt [n,21,3] float32; sums float64[2]. */
+int umt_mpjpe_accumulate(const float* pred, const float* gt, const uint8_t* valid, int n,
+                         double* sums, void* stream);
+
+/* Keypoint acceleration (load_eval.py:29-44): pts [n_seq, T, 21, 3], valid [n_seq, T];
+ * sums[0] += sum of mean_21 |p[t] + p[t+2] - 2 p[t+1]| over t with three consecutive valid
+ * frames; sums[1] += their count. */
+int umt_accel_accumulate(const float* pts, const uint8_t* valid, int n_seq, int T, double* sums,
+                         void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UMETRACK_B200_H */

@@ -1,0 +1,77 @@
+"""Stage (b) parity, part 1: the tensor-core backbone against the oracle, layer by layer."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import umetrack_oracle as O
+from umetrack_b200 import synthetic
+from umetrack_b200.model import UmeTrackModel
+from tests.helpers import golden
+
+pytestmark = pytest.mark.gpu
+
+# execution-order index of the conv that ends each block -> oracle tap name
+BLOCK_END = {}
+_i = 0
+for _li, _n in enumerate((2, 3, 5, 2)):
+    for _b in range(_n):
+        BLOCK_END[_i + 1] = f"layer{_li + 1}.{_b}"
+        _i += 2
+
+
+@pytest.fixture(scope="module")
+def setup():
+    sd = synthetic.make_state_dict(0)
+    model = UmeTrackModel(sd).to("cuda")
+    imgs = synthetic.make_model_batch(5, seed=100)["left_images"][:9]   # 9 crops: ragged vs tile sizes
+    taps = {}
+    with torch.no_grad():
+        feats = O.backbone_forward(sd, imgs, taps)
+    return sd, model, imgs, taps, feats
+
+
+@pytest.mark.parametrize("layer", list(range(30)))
+def test_each_conv_tensor_core_vs_cuda_core_and_oracle(setup, layer):
+    sd, model, imgs, taps, _ = setup
+    simt, umma = model.debug_layer(layer, imgs)
+    simt, umma = simt.cpu(), umma.cpu()
+    scale = float(simt.abs().max()) + 1e-6
+    # same operands, same program: only accumulation order and the dropped lo*lo term differ
+    assert float((simt - umma).abs().max()) <= 2e-5 * scale, f"layer {layer}: tensor-core != cuda-core"
+    if layer in BLOCK_END:
+        ref = taps[BLOCK_END[layer]]
+        assert umma.shape == ref.shape
+        assert float((umma - ref).abs().max()) <= 2e-4 * (float(ref.abs().max()) + 1e-6), \
+            f"layer {layer} ({BLOCK_END[layer]}) differs from the oracle"
+
+
+def test_backbone_features_vs_reference_golden(setup):
+    sd, model, imgs, taps, feats = setup
+    out = model.encode(imgs).cpu()
+    assert out.shape == (9, 72, 6, 6)
+    assert float((out - feats).abs().max()) <= 3e-4 * float(feats.abs().max())
+    g = golden("model_golden.npz")["k_backbone_feats_step0"]
+    b = synthetic.make_model_batch(6, seed=100, single_view_every=3)
+    got = model.encode(b["left_images"][:3]).cpu().numpy()
+    assert np.abs(got - g).max() <= 3e-4 * np.abs(g).max()
+    assert model.last_launch_count == 32   # stem + 30 convs + projection
+
+
+def test_chunking_and_batch_independence(setup):
+    sd, _, imgs, _, feats = setup
+    small = UmeTrackModel(sd, chunk_images=8).to("cuda")   # 9 images -> two encoder passes
+    out = small.encode(imgs).cpu()
+    assert float((out - feats).abs().max()) <= 3e-4 * float(feats.abs().max())
+    one = small.encode(imgs[4:5]).cpu()
+    assert torch.equal(one[0], out[4])
+
+
+def test_bf16_mode_reports_its_error(setup):
+    sd, model, imgs, _, feats = setup
+    model.set_mode("bf16")
+    try:
+        out = model.encode(imgs).cpu()
+    finally:
+        model.set_mode("fp32")
+    rel = float((out - feats).abs().max()) / float(feats.abs().max())
+    assert 1e-4 < rel < 8e-2, rel   # bf16 really is lower precision, but not garbage

@@ -1,0 +1,107 @@
+"""Stage (b) parity, part 2: full model outputs against vectors from the unmodified reference."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import umetrack_oracle as O
+from umetrack_b200 import hand_model as hmod
+from umetrack_b200 import synthetic
+from umetrack_b200.model import InputFrameData, InputFrameDesc, InputSkeletonData, UmeTrackModel, load_pretrained_model
+from umetrack_b200.skinning import fk_landmarks_device
+from tests.helpers import golden, hm_dict
+
+pytestmark = pytest.mark.gpu
+KEYPOINT_TOL_MM = 0.05
+
+
+def _inputs(b, dev="cuda"):
+    fd = InputFrameData(b["left_images"].to(dev), b["intrinsics"].to(dev), b["extrinsics_xf"].to(dev))
+    desc = InputFrameDesc(b["sample_range"].to(dev), b["memory_idx"].to(dev), b["use_memory"].to(dev), b["hand_idx"].to(dev))
+    return fd, desc
+
+
+def _keypoints_mm(model_hm, ja, wr_m):
+    wr = wr_m.clone().float().cuda()
+    wr[:, :3, 3] *= 1000.0
+    return fk_landmarks_device(model_hm, ja.float().cuda(), wr).cpu()
+
+
+def test_known_skeleton_head_two_steps_mixed_views(tmp_path):
+    g = golden("model_golden.npz")
+    sd = synthetic.make_state_dict(0)
+    path = tmp_path / "pretrained_weights.torch"
+    torch.save(sd, str(path))
+    model = load_pretrained_model(str(path))      # same file format as the reference
+    model.eval()
+    model.to("cuda")
+    hm = hmod.load_hand_model_from_dict(hm_dict())
+    skel = InputSkeletonData(hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None])
+    for step, use_mem in enumerate((False, True)):
+        b = synthetic.make_model_batch(6, seed=100 + step, single_view_every=3)
+        b["use_memory"][:] = use_mem
+        fd, desc = _inputs(b)
+        out = model.regress_pose_use_skeleton(fd, desc, skel)
+        ja, wr, sg = out.joint_angles.cpu(), out.wrist_xfs.cpu(), out.landmark_uncertainty_sigmas.cpu()
+        assert out.skel_scales is None
+        assert np.abs(ja.numpy() - g[f"k_joint_angles_{step}"]).max() < 2e-4
+        assert np.abs(wr.numpy() - g[f"k_wrist_xfs_{step}"]).max() < 2e-5          # metres
+        assert np.abs(sg.numpy() - g[f"k_sigmas_{step}"]).max() < 2e-4
+        kp = _keypoints_mm(hm, ja, wr)
+        kp_ref = _keypoints_mm(hm, torch.from_numpy(g[f"k_joint_angles_{step}"]), torch.from_numpy(g[f"k_wrist_xfs_{step}"]))
+        assert float((kp - kp_ref).abs().max()) < KEYPOINT_TOL_MM
+    assert np.abs(model._mem_features.cpu().numpy() - g["k_mem_after"]).max() < 2e-4
+
+
+def test_unknown_skeleton_head_and_single_view_rejection():
+    g = golden("model_golden.npz")
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda")
+    for step, use_mem in enumerate((False, True)):
+        b = synthetic.make_model_batch(4, seed=200 + step)
+        b["use_memory"][:] = use_mem
+        out = model.regress_pose_pred_skel_scale(*_inputs(b))
+        assert np.abs(out.skel_scales.cpu().numpy() - g[f"u_scales_{step}"]).max() < 2e-5
+        assert np.abs(out.wrist_xfs.cpu().numpy() - g[f"u_wrist_xfs_{step}"]).max() < 2e-5
+        assert np.abs(out.joint_angles.cpu().numpy() - g[f"u_joint_angles_{step}"]).max() < 2e-4
+    b = synthetic.make_model_batch(3, seed=5, single_view_every=3)
+    with pytest.raises(AssertionError):
+        model.regress_pose_pred_skel_scale(*_inputs(b))
+
+
+def test_large_batch_against_oracle_and_memory_slots():
+    """64 hand-frames, permuted memory slots, three steps; compared with the oracle on CPU."""
+    sd = synthetic.make_state_dict(0)
+    model = UmeTrackModel(sd, chunk_images=64).to("cuda")   # 128 crops -> 2 encoder chunks
+    orc = O.OracleModel(sd)
+    hm = hmod.load_hand_model_from_dict(hm_dict())
+    ax, rest = hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None]
+    perm = torch.from_numpy(np.random.default_rng(1).permutation(64))
+    for step in range(3):
+        b = synthetic.make_model_batch(64, seed=300 + step)
+        b["memory_idx"] = perm.clone()
+        b["use_memory"][:] = step > 0
+        if step == 2:
+            b["use_memory"][::5] = False   # some hands lose tracking: their memory is zeroed
+        out = model.regress_pose_use_skeleton(*_inputs(b), InputSkeletonData(ax, rest))
+        ref = orc.regress_pose_use_skeleton(b["left_images"], b["intrinsics"], b["extrinsics_xf"], b["sample_range"],
+                                            b["memory_idx"], b["use_memory"], b["hand_idx"], ax, rest)
+        kp = _keypoints_mm(hm, out.joint_angles.cpu(), out.wrist_xfs.cpu())
+        kp_ref = _keypoints_mm(hm, ref["joint_angles"], ref["wrist_xfs"])
+        assert float((kp - kp_ref).abs().max()) < KEYPOINT_TOL_MM, f"step {step}"
+    assert float((model._mem_features.cpu() - orc.state.mem).abs().max()) < 5e-4
+
+
+def test_errors_are_loud():
+    sd = synthetic.make_state_dict(0)
+    bad = dict(sd)
+    bad.pop("_regressor_u._pose_regression_layers.2.bias")
+    with pytest.raises(RuntimeError, match="Missing key"):
+        UmeTrackModel(bad)
+    bad = dict(sd)
+    bad["_temporal._temporal_module.0.weight"] = torch.zeros(90, 91, 1, 1)
+    with pytest.raises(RuntimeError, match="size mismatch"):
+        UmeTrackModel(bad)
+    m = UmeTrackModel(sd)
+    with pytest.raises(RuntimeError):
+        m.to("cpu")
+    with pytest.raises(RuntimeError):
+        m.encode(torch.zeros(1, 96, 96))   # no .to('cuda') yet

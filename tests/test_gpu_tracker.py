@@ -1,0 +1,50 @@
+"""End-to-end tracker parity with the reference's per-frame loop (run_eval_known_skeleton.py:48-102)."""
+import numpy as np
+import pytest
+import torch
+
+from umetrack_b200 import hand_model as hmod
+from umetrack_b200 import synthetic
+from umetrack_b200.evaluation import calibrate_scale, track_recording
+from umetrack_b200.hand_tracker import HandTracker, HandTrackerOpts, TrackingResult
+from umetrack_b200.metrics import MetricSums
+from umetrack_b200.model import UmeTrackModel
+from tests.helpers import golden, hm_dict
+
+pytestmark = pytest.mark.gpu
+
+
+def test_known_skeleton_recording_matches_reference():
+    g = golden("tracker_golden.npz")
+    labels, frames = synthetic.make_recording(hm_dict(), seed=3, n_frames=12)
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda")
+    sums = MetricSums("cuda")
+    res = track_recording(model, labels, frames, sums=sums)
+    assert np.array_equal(res["valid_tracking"], g["valid"])        # includes the confidence dropouts
+    d = np.abs(res["tracked_keypoints"] - g["tracked"])[g["valid"]]
+    assert d.max() < 0.05, f"keypoints differ by {d.max()} mm"       # north_star: 0.05 mm
+    assert np.abs(res["gt_keypoints"] - g["gt"]).max() < 0.05
+    assert abs(res["per_frame_mean_error"].mean() - g["per_frame_error"].mean()) < 0.01   # MPJPE gate
+    assert abs(sums.result()["mpjpe"] - g["per_frame_error"].mean()) < 0.01
+
+
+def test_empty_crop_cameras_resets_history():
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda")
+    tr = HandTracker(model, HandTrackerOpts())
+    tr._valid_tracking_history[:] = True
+    out = tr.track_frame(None, None, {})
+    assert out == TrackingResult() and not tr._valid_tracking_history.any()
+    assert tr.gen_crop_cameras([], [], None, {}, 1) == {}
+
+
+def test_unknown_skeleton_calibration_matches_reference():
+    g = golden("calibration_golden.npz")["scales"]
+    labels, frames = synthetic.make_recording(hm_dict(), seed=3, n_frames=12)
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda")
+    generic = hmod.load_hand_model_from_dict(hm_dict())
+    scaled, mean_scale, scales = calibrate_scale(model, labels, frames, generic, n_calibration_samples=30)
+    ref = g[~np.isnan(g)]
+    assert len(scales) == len(ref)
+    assert np.abs(scales - ref).max() < 1e-4
+    assert abs(mean_scale - ref.mean()) < 1e-4
+    assert torch.allclose(scaled.joint_rest_positions, generic.joint_rest_positions * mean_scale)

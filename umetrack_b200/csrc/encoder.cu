@@ -1,0 +1,894 @@
+// Stage (b), part 1: the per-view CNN encoder (30 convolutions, 99 % of the FLOPs) as
+// implicit-GEMM convolutions on the 5th-generation tensor cores (tcgen05.mma, accumulators in
+// TMEM), plus the stem (conv 1->32 + BN + ReLU + 2x2 max-pool) and the 256->72 projection on CUDA
+// cores.  Reference: lib/models/backbone_resnet.py:14-158, lib/models/model_utils.py:107-138.
+//
+// How a 3x3 convolution becomes a GEMM without materialising im2col
+// -----------------------------------------------------------------
+// Activations use the "planar flat" layout described in model.cuh: in that layout tap (dy,dx) of
+// output position q is input position q + dy*(W+1) + dx for EVERY q, so the A operand of tap t is
+// the same shared-memory patch viewed through a descriptor whose start address is moved by
+// shift_t rows.  A CTA therefore loads each 16-channel slice of its input patch ONCE (one
+// contiguous cp.async.bulk per 8-channel plane, no tensor map needed) and issues nine
+// M=128 x N=Cout x K=16 MMAs per 128-row sub-tile against it.  The UMMA shared-memory layout is
+// the no-swizzle K-major canonical layout: 8 rows x 16 bytes core matrices, SBO = 128 bytes
+// between 8-row groups, LBO = one plane between the two 8-channel halves of a K=16 step; a row
+// shift is then a plain +16-byte-per-row change of the descriptor start address.
+// Stride-2 convolutions read four parity-phase copies of their input (written by the producing
+// layer's epilogue), for which every tap is again a constant shift (0 or -1 rows/columns); the
+// 1x1 stride-2 downsample branch of a block is folded into the same accumulator as extra K.
+//
+// Numerics
+// --------
+// UMT_MODE_FP32_EQUIV keeps every activation and weight as a bf16 pair (hi, lo = x - hi) and
+// issues three products per K step, hi*hi + hi*lo + lo*hi, accumulating in fp32 in TMEM
+// (relative error ~2^-17 per product).  UMT_MODE_BF16 issues only hi*hi.
+//
+// Warp roles (256 threads): warp 0 lane 0 = A-patch producer, warp 1 lane 0 = weight-slab
+// producer, warp 2 = TMEM allocator + single-thread MMA issuer, warps 4..7 = epilogue
+// (tcgen05.ld -> bias/residual/ReLU -> bf16 split -> coalesced 16-byte stores).
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "model.cuh"
+
+namespace umt {
+
+static const int kStageHW[4] = {48, 24, 12, 6};
+static const int kStageC[4] = {32, 64, 128, 256};
+static const int kStageBlocks[4] = {2, 3, 5, 2};
+
+// ------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
+                                         uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_NONE: start address, LBO (byte distance of
+// the two 8-element K halves), SBO (byte distance of consecutive 8-row groups), version 1.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
+
+// split 8 floats into 8 bf16 hi (+ 8 bf16 lo) and store them as 16-byte rows
+template <bool SPLIT>
+__device__ __forceinline__ void store_row8(const FlatTensor& t, int plane, long long row,
+                                           const float* v) {
+  uint8_t* p = t.base + (long long)plane * t.plane_stride + (t.guard + row) * 16;
+  uint4 h;
+  h.x = pack_bf16x2(v[0], v[1]);
+  h.y = pack_bf16x2(v[2], v[3]);
+  h.z = pack_bf16x2(v[4], v[5]);
+  h.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(p) = h;
+  if (SPLIT) {
+    uint4 l;
+    l.x = pack_bf16x2(v[0] - bf16_lo(h.x), v[1] - bf16_hi(h.x));
+    l.y = pack_bf16x2(v[2] - bf16_lo(h.y), v[3] - bf16_hi(h.y));
+    l.z = pack_bf16x2(v[4] - bf16_lo(h.z), v[5] - bf16_hi(h.z));
+    l.w = pack_bf16x2(v[6] - bf16_lo(h.w), v[7] - bf16_hi(h.w));
+    *reinterpret_cast<uint4*>(p + t.lo_offset) = l;
+  }
+}
+
+template <bool SPLIT>
+__device__ __forceinline__ void load_row8(const FlatTensor& t, int plane, long long row, float* v) {
+  const uint8_t* p = t.base + (long long)plane * t.plane_stride + (t.guard + row) * 16;
+  uint4 h = *reinterpret_cast<const uint4*>(p);
+  v[0] = bf16_lo(h.x); v[1] = bf16_hi(h.x); v[2] = bf16_lo(h.y); v[3] = bf16_hi(h.y);
+  v[4] = bf16_lo(h.z); v[5] = bf16_hi(h.z); v[6] = bf16_lo(h.w); v[7] = bf16_hi(h.w);
+  if (SPLIT) {
+    uint4 l = *reinterpret_cast<const uint4*>(p + t.lo_offset);
+    v[0] += bf16_lo(l.x); v[1] += bf16_hi(l.x); v[2] += bf16_lo(l.y); v[3] += bf16_hi(l.y);
+    v[4] += bf16_lo(l.z); v[5] += bf16_hi(l.z); v[6] += bf16_lo(l.w); v[7] += bf16_hi(l.w);
+  }
+}
+
+// position -> (valid, destination tensor index, destination row)
+struct OutPos {
+  bool valid;
+  int tensor;
+  long long row;
+};
+__device__ __forceinline__ OutPos map_output(long long q, int H, int W, int n_pos, int phase_out) {
+  OutPos o;
+  const int Wp = W + 1, S = (H + 1) * Wp;
+  const int img = (int)(q / S);
+  const int rem = (int)(q - (long long)img * S);
+  const int y = rem / Wp, x = rem - y * Wp;
+  o.valid = (q < n_pos) && (x < W) && (y < H);
+  if (!phase_out) {
+    o.tensor = 0;
+    o.row = q;
+  } else {
+    const int W2p = (W >> 1) + 1, S2 = ((H >> 1) + 1) * W2p;
+    o.tensor = ((y & 1) << 1) | (x & 1);
+    o.row = (long long)img * S2 + (y >> 1) * W2p + (x >> 1);
+  }
+  return o;
+}
+
+// ------------------------------------------------------------------------------------------
+// The implicit-GEMM convolution kernel
+// ------------------------------------------------------------------------------------------
+constexpr int kConvThreads = 256;
+
+template <int COUT, bool SPLIT>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_umma_kernel(const __grid_constant__ ConvParams P) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 1000);
+  float* s_bias = reinterpret_cast<float*>(smem + 1024);
+  constexpr int kBiasBytes = ((COUT * 4 + 127) / 128) * 128;
+  const int n_a = P.n_a, n_b = P.n_b;
+  const uint32_t a_plane_bytes = (uint32_t)P.patch_rows * 16u;
+  const uint32_t a_stage_bytes = a_plane_bytes * (SPLIT ? 4u : 2u);
+  const uint32_t a_stage_stride = (a_stage_bytes + 127u) & ~127u;
+  constexpr uint32_t kBHalf = 2u * COUT * 16u;            // one of {w_hi, w_lo}: 2 planes
+  constexpr uint32_t kBSlabGlobal = 2u * kBHalf;          // packed slab always holds hi and lo
+  constexpr uint32_t kBStage = SPLIT ? 2u * kBHalf : kBHalf;
+  uint8_t* a_base = smem + 1024 + kBiasBytes;
+  uint8_t* b_base = a_base + (size_t)n_a * a_stage_stride;
+
+  // barrier indices
+  const uint32_t bar0 = smem_u32(bars);
+  auto a_full = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+  auto a_empty = [&](int i) { return bar0 + 8u * (uint32_t)(n_a + i); };
+  auto b_full = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + i); };
+  auto b_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + n_b + i); };
+  const uint32_t acc_full = bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long q0 = (long long)blockIdx.x * P.S * 128;
+  const uint32_t tmem_cols = (uint32_t)(P.S * COUT) <= 32u ? 32u
+                             : (uint32_t)(P.S * COUT) <= 64u ? 64u
+                             : (uint32_t)(P.S * COUT) <= 128u ? 128u
+                             : (uint32_t)(P.S * COUT) <= 256u ? 256u : 512u;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2 * n_a + 2 * n_b + 1; ++i) mbar_init(bar0 + 8u * i, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_slot)),
+                 "r"(tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp == 3) {
+    for (int c = lane; c < COUT; c += 32) s_bias[c] = P.bias[c];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ===== A-patch producer: one 16-channel slice (2 planes hi [+2 planes lo]) per stage =====
+    for (int i = 0; i < P.n_stages; ++i) {
+      const int slot = i % n_a;
+      const uint32_t ph = (uint32_t)(i / n_a) & 1u;
+      mbar_wait(a_empty(slot), ph ^ 1u);
+      mbar_expect_tx(a_full(slot), a_stage_bytes);
+      const FlatTensor& T = P.src[P.st_src[i]];
+      const uint8_t* g = T.base + (long long)(2 * P.st_chunk[i]) * T.plane_stride +
+                         ((long long)T.guard + q0 + P.lo_shift) * 16;
+      const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride);
+      bulk_g2s(dst, g, a_plane_bytes, a_full(slot));
+      bulk_g2s(dst + a_plane_bytes, g + T.plane_stride, a_plane_bytes, a_full(slot));
+      if (SPLIT) {
+        bulk_g2s(dst + 2 * a_plane_bytes, g + T.lo_offset, a_plane_bytes, a_full(slot));
+        bulk_g2s(dst + 3 * a_plane_bytes, g + T.lo_offset + T.plane_stride, a_plane_bytes,
+                 a_full(slot));
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== weight-slab producer: one (stage, tap) slab per B stage =====
+    int k = 0;
+    for (int i = 0; i < P.n_stages; ++i) {
+      for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
+        const int slot = k % n_b;
+        const uint32_t ph = (uint32_t)(k / n_b) & 1u;
+        mbar_wait(b_empty(slot), ph ^ 1u);
+        mbar_expect_tx(b_full(slot), kBStage);
+        bulk_g2s(smem_u32(b_base + (size_t)slot * kBStage), P.weights + (size_t)k * kBSlabGlobal,
+                 kBStage, b_full(slot));
+      }
+    }
+  } else if (warp == 2 && lane == 0) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | (1u << 7) /* A = bf16 */ |
+                               (1u << 10) /* B = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
+                               ((128u >> 4) << 24);
+    int k = 0;
+    uint32_t any = 0;
+    for (int i = 0; i < P.n_stages; ++i) {
+      const int aslot = i % n_a;
+      mbar_wait(a_full(aslot), (uint32_t)(i / n_a) & 1u);
+      const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
+      for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
+        const int bslot = k % n_b;
+        mbar_wait(b_full(bslot), (uint32_t)(k / n_b) & 1u);
+        tc_fence_after();
+        const uint32_t b_s = smem_u32(b_base + (size_t)bslot * kBStage);
+        const uint64_t b_hi = umma_desc(b_s, COUT * 16u, 128u);
+        const uint64_t b_lo = umma_desc(b_s + kBHalf, COUT * 16u, 128u);
+        const int shift = (int)P.tap_shift[P.st_tap0[i] + t] - P.lo_shift;
+        for (int s = 0; s < P.S; ++s) {
+          const uint32_t a_row = a_s + (uint32_t)(s * 128 + shift) * 16u;
+          const uint64_t a_hi = umma_desc(a_row, a_plane_bytes, 128u);
+          const uint32_t d = tmem_base + (uint32_t)(s * COUT);
+          tc_mma_bf16(d, a_hi, b_hi, idesc, any);
+          if (SPLIT) {
+            const uint64_t a_lo = umma_desc(a_row + 2u * a_plane_bytes, a_plane_bytes, 128u);
+            tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
+            tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
+          }
+        }
+        any = 1u;
+        tc_commit(b_empty(bslot));
+      }
+      tc_commit(a_empty(aslot));
+    }
+    tc_commit(acc_full);
+  } else if (warp >= 4) {
+    // ===== epilogue: TMEM -> registers -> bias / residual / ReLU -> split bf16 -> global =====
+    mbar_wait(acc_full, 0u);
+    tc_fence_after();
+    const int lgrp = warp & 3;  // TMEM lane group this warp may read
+    const bool has_res = P.res.base != nullptr;
+    for (int s = 0; s < P.S; ++s) {
+      const long long q = q0 + s * 128 + lgrp * 32 + lane;
+      const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
+      const FlatTensor& T = P.out[o.tensor];
+#pragma unroll 1
+      for (int c0 = 0; c0 < COUT; c0 += 16) {
+        uint32_t v[16];
+        tc_ld16(tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)(s * COUT + c0), v);
+        tc_ld_wait();
+        if (o.valid) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e];
+            if (has_res) {
+              float r[8];
+              load_row8<SPLIT>(P.res, (c0 >> 3) + h, q, r);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] += r[e];
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
+            store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(tmem_cols)
+                 : "memory");
+  }
+}
+
+static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
+  size_t bias = ((size_t)cout * 4 + 127) / 128 * 128;
+  size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
+  size_t b = (size_t)2 * cout * 16 * (split ? 2 : 1);
+  return 1024 + bias + a * p.n_a + b * p.n_b;
+}
+
+template <int COUT, bool SPLIT>
+static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
+  const size_t smem = conv_smem_bytes(p, COUT, SPLIT);
+  UMT_CUDA_TRY(cudaFuncSetAttribute(conv_umma_kernel<COUT, SPLIT>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int mc = p.S * 128;
+  const int tiles = (p.n_pos + mc - 1) / mc;
+  conv_umma_kernel<COUT, SPLIT><<<tiles, kConvThreads, smem, st>>>(p);
+  return check_launch("conv_umma_kernel");
+}
+
+static int launch_conv(const ConvParams& p, int cout, bool split, cudaStream_t st) {
+  switch (cout) {
+    case 32: return split ? launch_conv_t<32, true>(p, st) : launch_conv_t<32, false>(p, st);
+    case 64: return split ? launch_conv_t<64, true>(p, st) : launch_conv_t<64, false>(p, st);
+    case 128: return split ? launch_conv_t<128, true>(p, st) : launch_conv_t<128, false>(p, st);
+    case 256: return split ? launch_conv_t<256, true>(p, st) : launch_conv_t<256, false>(p, st);
+  }
+  return fail(UMT_ERR_UNSUPPORTED, "conv: unsupported Cout %d", cout);
+}
+
+// ------------------------------------------------------------------------------------------
+// CUDA-core check kernel (test hook): same program, same packed weights, plain fp32 FMAs,
+// dense [n, C, H, W] float output.  One thread per (position, output channel).
+// ------------------------------------------------------------------------------------------
+__global__ void conv_simt_check_kernel(const ConvParams P, int cout, int split,
+                                       float* __restrict__ out /* [n,cout,H,W] */) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int Wp = P.W + 1, S = (P.H + 1) * Wp;
+  const long long total = (long long)P.n_pos * cout;
+  if (idx >= total) return;
+  const int co = (int)(idx % cout);
+  const long long q = idx / cout;
+  const int img = (int)(q / S), rem = (int)(q % S), y = rem / Wp, x = rem % Wp;
+  if (x >= P.W || y >= P.H) return;
+  float acc = 0.f;
+  int k = 0;
+  const size_t half = (size_t)2 * cout * 16, slab = 2 * half;
+  for (int i = 0; i < P.n_stages; ++i) {
+    const FlatTensor& T = P.src[P.st_src[i]];
+    for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
+      const long long row = q + P.tap_shift[P.st_tap0[i] + t];
+      const uint8_t* w = P.weights + (size_t)k * slab;
+      for (int pl = 0; pl < 2; ++pl) {
+        const uint8_t* ap = T.base + (long long)(2 * P.st_chunk[i] + pl) * T.plane_stride +
+                            (T.guard + row) * 16;
+        const __nv_bfloat16* ah = reinterpret_cast<const __nv_bfloat16*>(ap);
+        const __nv_bfloat16* al = reinterpret_cast<const __nv_bfloat16*>(ap + T.lo_offset);
+        const __nv_bfloat16* wh = reinterpret_cast<const __nv_bfloat16*>(w + (size_t)pl * cout * 16 + (size_t)co * 16);
+        const __nv_bfloat16* wl = reinterpret_cast<const __nv_bfloat16*>(w + half + (size_t)pl * cout * 16 + (size_t)co * 16);
+        for (int e = 0; e < 8; ++e) {
+          float a = __bfloat162float(ah[e]), b = __bfloat162float(wh[e]);
+          if (split) {
+            a += __bfloat162float(al[e]);
+            b += __bfloat162float(wl[e]);
+          }
+          acc = fmaf(a, b, acc);
+        }
+      }
+    }
+  }
+  acc += P.bias[co];
+  if (P.res.base) {
+    const uint8_t* rp = P.res.base + (long long)(co >> 3) * P.res.plane_stride + (P.res.guard + q) * 16;
+    float r = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rp)[co & 7]);
+    if (split) r += __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rp + P.res.lo_offset)[co & 7]);
+    acc += r;
+  }
+  acc = fmaxf(acc, 0.f);
+  out[(((size_t)img * cout + co) * P.H + y) * P.W + x] = acc;
+}
+
+// planar flat (or 4 parity-phase tensors) -> dense [n, C, H, W] float (test hook)
+__global__ void densify_kernel(const ConvParams P, int C, int split, float* __restrict__ out) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)P.n_pos * C;
+  if (idx >= total) return;
+  const int c = (int)(idx % C);
+  const long long q = idx / C;
+  const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
+  if (!o.valid) return;
+  const FlatTensor& T = P.out[o.tensor];
+  const uint8_t* p = T.base + (long long)(c >> 3) * T.plane_stride + (T.guard + o.row) * 16;
+  float v = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[c & 7]);
+  if (split) v += __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p + T.lo_offset)[c & 7]);
+  const int Wp = P.W + 1, S = (P.H + 1) * Wp;
+  const int img = (int)(q / S), rem = (int)(q % S), y = rem / Wp, x = rem % Wp;
+  out[(((size_t)img * C + c) * P.H + y) * P.W + x] = v;
+}
+
+// ------------------------------------------------------------------------------------------
+// Stem: conv3x3(1->32, bias) + BN + ReLU + MaxPool2 (lib/models/model_utils.py:119-124), BN folded.
+// One thread per pooled output pixel; writes the 32 channels as four 16-byte rows (hi [+ lo]).
+// ------------------------------------------------------------------------------------------
+template <bool SPLIT>
+__global__ void __launch_bounds__(256)
+stem_kernel(const float* __restrict__ images, int n_img, const float* __restrict__ w /* [32][9] */,
+            const float* __restrict__ b, FlatTensor out) {
+  __shared__ float sw[32 * 9];
+  __shared__ float sb[32];
+  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
+  if (threadIdx.x < 32) sb[threadIdx.x] = b[threadIdx.x];
+  __syncthreads();
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)n_img * 48 * 48;
+  if (idx >= total) return;
+  const int img = (int)(idx / 2304), rem = (int)(idx % 2304), oy = rem / 48, ox = rem % 48;
+  const float* im = images + (size_t)img * 9216;
+  float patch[4][4];
+#pragma unroll
+  for (int dy = 0; dy < 4; ++dy) {
+#pragma unroll
+    for (int dx = 0; dx < 4; ++dx) {
+      const int yy = 2 * oy + dy - 1, xx = 2 * ox + dx - 1;
+      patch[dy][dx] = (yy >= 0 && yy < 96 && xx >= 0 && xx < 96) ? __ldg(im + yy * 96 + xx) : 0.f;
+    }
+  }
+  const long long row = (long long)img * 49 * 49 + oy * 49 + ox;
+#pragma unroll 1
+  for (int g = 0; g < 4; ++g) {
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = g * 8 + e;
+      float best = 0.f;  // ReLU then max == max(0, .)
+#pragma unroll
+      for (int py = 0; py < 2; ++py) {
+#pragma unroll
+        for (int px = 0; px < 2; ++px) {
+          float a = sb[c];
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) a = fmaf(patch[py + ky][px + kx], sw[c * 9 + ky * 3 + kx], a);
+          best = fmaxf(best, a);
+        }
+      }
+      v[e] = best;
+    }
+    store_row8<SPLIT>(out, g, row, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Projection conv1x1(256->72, bias) (lib/models/model_utils.py:134): planar flat (6x6x256) ->
+// dense float32 [n,72,6,6].  One CTA per image: activations in shared memory, each thread
+// produces one output channel for six pixels (weights read once per six FMAs).
+// ------------------------------------------------------------------------------------------
+template <bool SPLIT>
+__global__ void __launch_bounds__(432)
+proj_kernel(FlatTensor in, int n_img, const float* __restrict__ w /* [72][256] */,
+            const float* __restrict__ b, float* __restrict__ out) {
+  __shared__ float sx[36][257];
+  const int img = blockIdx.x;
+  for (int i = threadIdx.x; i < 36 * 32; i += blockDim.x) {
+    const int pix = i / 32, plane = i % 32;
+    const long long row = (long long)img * 49 + (pix / 6) * 7 + (pix % 6);
+    float v[8];
+    load_row8<SPLIT>(in, plane, row, v);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sx[pix][plane * 8 + e] = v[e];
+  }
+  __syncthreads();
+  const int co = threadIdx.x % 72, pg = threadIdx.x / 72;  // pixel group of 6
+  float acc[6];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) acc[j] = b[co];
+  const float* wr = w + (size_t)co * 256;
+  for (int ci = 0; ci < 256; ++ci) {
+    const float ww = __ldg(wr + ci);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) acc[j] = fmaf(sx[pg * 6 + j][ci], ww, acc[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) out[((size_t)img * 72 + co) * 36 + pg * 6 + j] = acc[j];
+}
+
+// ------------------------------------------------------------------------------------------
+// Host side: BN folding, operand packing, programs, workspace layout, layer schedule
+// ------------------------------------------------------------------------------------------
+static inline uint16_t f2bf(float f) {  // round to nearest even
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7F800000u) == 0x7F800000u) return (uint16_t)(u >> 16);
+  u += 0x7FFFu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+static inline float bf2f(uint16_t h) {
+  uint32_t u = (uint32_t)h << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+struct Folded {           // conv weight with BatchNorm folded in: w'[co][ci][k], b'[co]
+  std::vector<float> w, b;
+  int cout, cin, ks;
+};
+
+static Folded fold_conv_bn(const float* w, const float* conv_bias, const float* gamma,
+                           const float* beta, const float* mean, const float* var, int cout,
+                           int cin, int ks) {
+  Folded f;
+  f.cout = cout; f.cin = cin; f.ks = ks;
+  f.w.resize((size_t)cout * cin * ks * ks);
+  f.b.resize(cout);
+  for (int co = 0; co < cout; ++co) {
+    float scale = 1.f, shift = 0.f;
+    if (gamma) {
+      // same arithmetic as eval-mode batch_norm: (x - mean) / sqrt(var + eps) * gamma + beta
+      scale = gamma[co] / std::sqrt(var[co] + 1e-5f);
+      shift = beta[co] - mean[co] * scale;
+    }
+    for (size_t i = 0; i < (size_t)cin * ks * ks; ++i)
+      f.w[(size_t)co * cin * ks * ks + i] = w[(size_t)co * cin * ks * ks + i] * scale;
+    f.b[co] = (conv_bias ? conv_bias[co] * scale : 0.f) + shift;
+  }
+  return f;
+}
+
+static const float* tensor_ptr(const float* const* t, const std::string& name) {
+  int i = tensor_index(name.c_str());
+  return i < 0 ? nullptr : t[i];
+}
+
+static Folded folded_from(const float* const* t, const std::string& conv, const std::string& bn,
+                          int cout, int cin, int ks, bool has_bias) {
+  return fold_conv_bn(tensor_ptr(t, conv + ".weight"), has_bias ? tensor_ptr(t, conv + ".bias") : nullptr,
+                      bn.empty() ? nullptr : tensor_ptr(t, bn + ".weight"),
+                      bn.empty() ? nullptr : tensor_ptr(t, bn + ".bias"),
+                      bn.empty() ? nullptr : tensor_ptr(t, bn + ".running_mean"),
+                      bn.empty() ? nullptr : tensor_ptr(t, bn + ".running_var"), cout, cin, ks);
+}
+
+// append one operand slab: [hi: plane0 [cout][8], plane1 [cout][8]] [lo: same]
+static void pack_slab(std::vector<uint16_t>& blob, const Folded& f, int chunk, int ky, int kx) {
+  const size_t base = blob.size();
+  blob.resize(base + (size_t)4 * f.cout * 8);
+  for (int pl = 0; pl < 2; ++pl)
+    for (int co = 0; co < f.cout; ++co)
+      for (int e = 0; e < 8; ++e) {
+        const int ci = chunk * 16 + pl * 8 + e;
+        const float v = f.w[(((size_t)co * f.cin + ci) * f.ks + ky) * f.ks + kx];
+        const uint16_t hi = f2bf(v);
+        const uint16_t lo = f2bf(v - bf2f(hi));
+        blob[base + ((size_t)pl * f.cout + co) * 8 + e] = hi;
+        blob[base + (size_t)2 * f.cout * 8 + ((size_t)pl * f.cout + co) * 8 + e] = lo;
+      }
+}
+
+static int env_int(const char* name, int dflt) {
+  const char* s = getenv(name);
+  return s ? atoi(s) : dflt;
+}
+
+// Build program + packed weights of one backbone convolution.
+static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds) {
+  ConvParams& p = L.prog;
+  memset(&p, 0, sizeof(p));
+  const int H = kStageHW[L.geom], W = H, Wp = W + 1;
+  p.H = H; p.W = W;
+  std::vector<uint16_t> blob;
+  int ns = 0, nt = 0, lo = 0, hi = 0;
+  auto add_tap = [&](int shift) {
+    p.tap_shift[nt++] = (short)shift;
+    lo = std::min(lo, shift);
+    hi = std::max(hi, shift);
+  };
+  if (L.stride == 1) {
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) add_tap((ky - 1) * Wp + (kx - 1));
+    for (int c = 0; c < main.cin / 16; ++c) {
+      p.st_src[ns] = 0; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = 9; p.st_tap0[ns] = 0;
+      ++ns;
+      for (int ky = 0; ky < 3; ++ky)
+        for (int kx = 0; kx < 3; ++kx) pack_slab(blob, main, c, ky, kx);
+    }
+    if (ds) {  // fused 1x1 stride-2 downsample: source 1 = parity-phase (0,0) of the block input
+      for (int c = 0; c < ds->cin / 16; ++c) {
+        p.st_src[ns] = 1; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = 1; p.st_tap0[ns] = 4;
+        ++ns;
+        pack_slab(blob, *ds, c, 0, 0);
+      }
+    }
+  } else {
+    // stride 2: tap (ky,kx) reads parity phase ((ky+1)&1, (kx+1)&1) shifted by -1 row/col iff k==0
+    int tap0[4];
+    for (int ph = 0; ph < 4; ++ph) {
+      tap0[ph] = nt;
+      const int py = ph >> 1, px = ph & 1;
+      for (int ky = 0; ky < 3; ++ky) {
+        if (((ky + 1) & 1) != py) continue;
+        for (int kx = 0; kx < 3; ++kx) {
+          if (((kx + 1) & 1) != px) continue;
+          add_tap((ky == 0 ? -1 : 0) * Wp + (kx == 0 ? -1 : 0));
+        }
+      }
+    }
+    for (int c = 0; c < main.cin / 16; ++c)
+      for (int ph = 0; ph < 4; ++ph) {
+        const int py = ph >> 1, px = ph & 1;
+        int cnt = 0;
+        for (int ky = 0; ky < 3; ++ky) {
+          if (((ky + 1) & 1) != py) continue;
+          for (int kx = 0; kx < 3; ++kx) {
+            if (((kx + 1) & 1) != px) continue;
+            pack_slab(blob, main, c, ky, kx);
+            ++cnt;
+          }
+        }
+        p.st_src[ns] = (uint8_t)ph; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = (uint8_t)cnt;
+        p.st_tap0[ns] = (uint8_t)tap0[ph];
+        ++ns;
+      }
+  }
+  if (ns > kMaxStages || nt > kMaxTaps) return fail(UMT_ERR_INVALID, "conv program too large");
+  p.n_stages = ns;
+  p.lo_shift = lo;
+  // tile shape: S sub-tiles so that S*Cout TMEM columns = 256 (two CTAs can share an SM)
+  int S = std::max(1, std::min(4, 256 / L.cout));
+  S = std::min(4, S * env_int("UMT_CONV_S_SCALE", 1));
+  while (S * L.cout > 512) S >>= 1;
+  p.S = S;
+  p.patch_rows = S * 128 + hi - lo;
+  p.phase_out = L.phase_out;
+  L.n_slabs = (int)(blob.size() / ((size_t)4 * L.cout * 8));
+  std::vector<float> bias = main.b;
+  if (ds) for (int i = 0; i < L.cout; ++i) bias[i] += ds->b[i];
+  UMT_CUDA_TRY(cudaMalloc(&L.d_weights, blob.size() * 2));
+  m->owned.push_back(L.d_weights);
+  UMT_CUDA_TRY(cudaMemcpy(L.d_weights, blob.data(), blob.size() * 2, cudaMemcpyHostToDevice));
+  L.d_bias = upload(m, bias);
+  if (!L.d_bias) return UMT_ERR_CUDA;
+  return UMT_OK;
+}
+
+int encoder_build(umt_model* m, const float* const* t) {
+  const std::string bb = "_feature_extractor._image_backbone.0._layers.";
+  m->convs.clear();
+  int cin = 32;
+  for (int g = 0; g < 4; ++g) {
+    const int cout = kStageC[g];
+    int cur = 0;  // index of the ping/pong buffer holding the block input
+    for (int b = 0; b < kStageBlocks[g]; ++b) {
+      const std::string pre = bb + std::to_string(g + 1) + "." + std::to_string(b);
+      const bool first_ds = (b == 0 && g > 0);
+      const bool last = (b == kStageBlocks[g] - 1);
+      ConvLayer c1, c2;
+      c1.cout = cout; c1.cin = first_ds ? cin : cout; c1.stride = first_ds ? 2 : 1; c1.geom = g;
+      c1.src_kind = first_ds ? 1 : 0; c1.src_buf = cur; c1.out_buf = 2; c1.res_buf = -1;
+      Folded f1 = folded_from(t, pre + ".conv1", pre + ".bn1", cout, c1.cin, 3, false);
+      UMT_TRY(build_conv(m, c1, f1, nullptr));
+      m->convs.push_back(c1);
+      c2.cout = cout; c2.cin = cout; c2.stride = 1; c2.geom = g; c2.src_kind = 0; c2.src_buf = 2;
+      c2.phase_out = (last && g < 3) ? 1 : 0;
+      Folded f2 = folded_from(t, pre + ".conv2", pre + ".bn2", cout, cout, 3, false);
+      if (first_ds) {
+        c2.ds_cin = cin;
+        c2.res_buf = -1;
+        c2.out_buf = 0;
+        Folded fd = folded_from(t, pre + ".downsample.0", pre + ".downsample.1", cout, cin, 1, false);
+        UMT_TRY(build_conv(m, c2, f2, &fd));
+        cur = 0;
+      } else {
+        c2.res_buf = cur;
+        c2.out_buf = 1 - cur;
+        UMT_TRY(build_conv(m, c2, f2, nullptr));
+        cur = 1 - cur;
+      }
+      m->convs.push_back(c2);
+    }
+    cin = cout;
+  }
+  // stem + projection (CUDA cores, float32)
+  Folded st = folded_from(t, bb + "0.0", bb + "0.1", 32, 1, 3, true);
+  m->tw.stem_w = upload(m, st.w);
+  m->tw.stem_b = upload(m, st.b);
+  Folded pj = folded_from(t, "_feature_extractor._image_backbone.1", "", 72, 256, 1, true);
+  m->tw.proj_w = upload(m, pj.w);
+  m->tw.proj_b = upload(m, pj.b);
+  if (!m->tw.stem_w || !m->tw.stem_b || !m->tw.proj_w || !m->tw.proj_b) return UMT_ERR_CUDA;
+  return UMT_OK;
+}
+
+// ---- workspace layout -------------------------------------------------------------------
+static long long plane_rows(int H, int n_img, int* guard_out) {
+  const int Wp = H + 1;
+  const int guard = ((Wp + 2 + 7) / 8) * 8;
+  const long long pos = (long long)n_img * Wp * Wp;
+  const long long padded = (pos + 511) / 512 * 512;
+  *guard_out = guard;
+  return guard + padded + guard + 8;
+}
+
+static size_t flat_bytes(int H, int C, int n_img) {
+  int g;
+  return (size_t)plane_rows(H, n_img, &g) * 16 * (C / 8) * 2;
+}
+
+static FlatTensor make_flat(uint8_t* base, int H, int C, int n_img) {
+  FlatTensor t;
+  int g;
+  const long long rows = plane_rows(H, n_img, &g);
+  t.base = base;
+  t.plane_stride = rows * 16;
+  t.lo_offset = t.plane_stride * (C / 8);
+  t.guard = g;
+  t.pad_ = 0;
+  return t;
+}
+
+size_t encoder_workspace_bytes(int chunk_images) {
+  size_t total = 0;
+  const int n = chunk_images;
+  for (int g = 0; g < 4; ++g) {
+    total += 3 * flat_bytes(kStageHW[g], kStageC[g], n);
+    if (g > 0) total += 4 * flat_bytes(kStageHW[g], kStageC[g - 1], n);
+  }
+  return (total + 255) & ~(size_t)255;
+}
+
+void encoder_bind(umt_model* m, uint8_t* base) {
+  const int n = m->chunk_images;
+  uint8_t* p = base;
+  for (int g = 0; g < 4; ++g) {
+    for (int b = 0; b < 3; ++b) {
+      m->buf[g][b] = make_flat(p, kStageHW[g], kStageC[g], n);
+      p += flat_bytes(kStageHW[g], kStageC[g], n);
+    }
+    if (g > 0)
+      for (int ph = 0; ph < 4; ++ph) {
+        m->phase[g][ph] = make_flat(p, kStageHW[g], kStageC[g - 1], n);
+        p += flat_bytes(kStageHW[g], kStageC[g - 1], n);
+      }
+  }
+}
+
+static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool split,
+                         ConvParams& p) {
+  p = L.prog;
+  const int g = L.geom;
+  if (L.src_kind == 1) {
+    for (int ph = 0; ph < 4; ++ph) p.src[ph] = m->phase[g][ph];
+  } else {
+    p.src[0] = m->buf[g][L.src_buf];
+    if (L.ds_cin) p.src[1] = m->phase[g][0];
+  }
+  if (L.phase_out) {
+    for (int ph = 0; ph < 4; ++ph) p.out[ph] = m->phase[g + 1][ph];
+  } else {
+    p.out[0] = m->buf[g][L.out_buf];
+  }
+  if (L.res_buf >= 0) p.res = m->buf[g][L.res_buf];
+  else p.res.base = nullptr;
+  p.weights = L.d_weights;
+  p.bias = L.d_bias;
+  p.n_pos = n_img * (p.H + 1) * (p.W + 1);
+  // pipeline depths from the shared-memory budget
+  const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", 100) * 1024;
+  const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
+  const size_t b = (size_t)2 * L.cout * 16 * (split ? 2 : 1);
+  const size_t fixed = 1024 + ((size_t)L.cout * 4 + 127) / 128 * 128;
+  int n_a = 3;
+  while (n_a > 2 && fixed + a * n_a + b * 4 > budget) --n_a;
+  long long nb = ((long long)budget - (long long)fixed - (long long)(a * n_a)) / (long long)b;
+  p.n_a = n_a;
+  p.n_b = (int)std::max(3LL, std::min(12LL, nb));
+}
+
+int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, float* features,
+                      int stop_after_layer, cudaStream_t st, cudaEvent_t* ev) {
+  if (!m->ws) return fail(UMT_ERR_INVALID, "no workspace bound (umt_model_bind_workspace)");
+  if (n_img <= 0 || n_img > m->chunk_images)
+    return fail(UMT_ERR_INVALID, "encoder chunk of %d images (capacity %d)", n_img, m->chunk_images);
+  const bool split = (mode == UMT_MODE_FP32_EQUIV);
+  const long long px = (long long)n_img * 2304;
+  const int blocks = (int)((px + 255) / 256);
+  if (ev) cudaEventRecord(ev[0], st);
+  if (split)
+    stem_kernel<true><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
+  else
+    stem_kernel<false><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
+  UMT_TRY(check_launch("stem_kernel"));
+  ++m->launches;
+  for (size_t i = 0; i < m->convs.size(); ++i) {
+    if (stop_after_layer >= 0 && (int)i > stop_after_layer) return UMT_OK;
+    ConvParams p;
+    fill_tensors(m, m->convs[i], n_img, split, p);
+    if (ev) cudaEventRecord(ev[1 + i], st);
+    UMT_TRY(launch_conv(p, m->convs[i].cout, split, st));
+    ++m->launches;
+  }
+  if (ev) cudaEventRecord(ev[31], st);
+  if (features) {
+    const ConvLayer& last = m->convs.back();
+    if (split)
+      proj_kernel<true><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);
+    else
+      proj_kernel<false><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);
+    UMT_TRY(check_launch("proj_kernel"));
+    ++m->launches;
+  }
+  if (ev) cudaEventRecord(ev[32], st);
+  return UMT_OK;
+}
+
+int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
+                        float* out_simt, float* out_umma, int* shape, cudaStream_t st) {
+  if (layer < 0 || layer >= (int)m->convs.size()) return fail(UMT_ERR_INVALID, "layer %d out of range", layer);
+  const bool split = (mode == UMT_MODE_FP32_EQUIV);
+  // inputs of `layer`: run everything before it
+  UMT_TRY(encoder_run_chunk(m, mode, images, n_img, nullptr, layer - 1, st, nullptr));
+  const ConvLayer& L = m->convs[layer];
+  ConvParams p;
+  fill_tensors(m, L, n_img, split, p);
+  if (shape) { shape[0] = L.cout; shape[1] = p.H; shape[2] = p.W; }
+  const long long total = (long long)p.n_pos * L.cout;
+  const int blocks = (int)((total + 255) / 256);
+  const size_t dense = (size_t)n_img * L.cout * p.H * p.W * sizeof(float);
+  if (out_simt) {
+    UMT_CUDA_TRY(cudaMemsetAsync(out_simt, 0, dense, st));
+    conv_simt_check_kernel<<<blocks, 256, 0, st>>>(p, L.cout, split ? 1 : 0, out_simt);
+    UMT_TRY(check_launch("conv_simt_check_kernel"));
+  }
+  if (out_umma) {
+    UMT_TRY(launch_conv(p, L.cout, split, st));
+    UMT_CUDA_TRY(cudaMemsetAsync(out_umma, 0, dense, st));
+    densify_kernel<<<blocks, 256, 0, st>>>(p, L.cout, split ? 1 : 0, out_umma);
+    UMT_TRY(check_launch("densify_kernel"));
+  }
+  return UMT_OK;
+}
+
+}  // namespace umt

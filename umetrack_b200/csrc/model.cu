@@ -1,0 +1,289 @@
+// Model handle, weight-tensor registry, workspace binding and the C ABI entry points of stage (b).
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "model.cuh"
+
+namespace umt {
+
+char* last_error_buffer() {
+  static thread_local char buf[512] = {0};
+  return buf;
+}
+
+// ---- weight tensor registry: the reference's state_dict (lib/models/model_loader.py:84-87) ----
+struct TensorInfo {
+  std::string name;
+  int64_t numel;
+};
+
+static void add_bn(std::vector<TensorInfo>& v, const std::string& p, int c) {
+  v.push_back({p + ".weight", c});
+  v.push_back({p + ".bias", c});
+  v.push_back({p + ".running_mean", c});
+  v.push_back({p + ".running_var", c});
+}
+
+static void add_block(std::vector<TensorInfo>& v, const std::string& p, int cin, int cout, bool ds) {
+  v.push_back({p + ".conv1.weight", (int64_t)cout * cin * 9});
+  add_bn(v, p + ".bn1", cout);
+  v.push_back({p + ".conv2.weight", (int64_t)cout * cout * 9});
+  add_bn(v, p + ".bn2", cout);
+  if (ds) {
+    v.push_back({p + ".downsample.0.weight", (int64_t)cout * cin});
+    add_bn(v, p + ".downsample.1", cout);
+  }
+}
+
+static const std::vector<TensorInfo>& registry() {
+  static std::vector<TensorInfo> v;
+  if (!v.empty()) return v;
+  const std::string b = "_feature_extractor._image_backbone.0._layers.";
+  v.push_back({b + "0.0.weight", 32 * 9});
+  v.push_back({b + "0.0.bias", 32});
+  add_bn(v, b + "0.1", 32);
+  const int blocks[4] = {2, 3, 5, 2}, planes[4] = {32, 64, 128, 256};
+  int cin = 32;
+  for (int g = 0; g < 4; ++g)
+    for (int k = 0; k < blocks[g]; ++k) {
+      add_block(v, b + std::to_string(g + 1) + "." + std::to_string(k), cin, planes[g], k == 0 && g > 0);
+      cin = planes[g];
+    }
+  v.push_back({"_feature_extractor._image_backbone.1.weight", 72 * 256});
+  v.push_back({"_feature_extractor._image_backbone.1.bias", 72});
+  const std::string f = "_feature_extractor._multi_view_fusion.";
+  v.push_back({f + "0.weight", 108 * 144});
+  v.push_back({f + "0.bias", 108});
+  add_bn(v, f + "1", 108);
+  v.push_back({f + "3.weight", 72 * 108});
+  v.push_back({f + "3.bias", 72});
+  add_bn(v, f + "4", 72);
+  v.push_back({f + "6.weight", 72 * 72});
+  v.push_back({f + "6.bias", 72});
+  for (int i = 0; i < 3; ++i) {
+    const std::string t = "_temporal._temporal_module." + std::to_string(2 * i);
+    v.push_back({t + ".weight", 90 * 90});
+    v.push_back({t + ".bias", 90});
+  }
+  v.push_back({"_skeleton_enc._layers.0.weight", 144 * 132});
+  v.push_back({"_skeleton_enc._layers.0.bias", 144});
+  add_bn(v, "_skeleton_enc._layers.2", 4);
+  const char* heads[2] = {"_regressor_k", "_regressor_u"};
+  const int hc[2] = {76, 72}, ho[2] = {62, 63};
+  for (int h = 0; h < 2; ++h) {
+    const std::string p = std::string(heads[h]) + "._pose_regression_layers.";
+    add_block(v, p + "0", hc[h], hc[h], false);
+    add_block(v, p + "1", hc[h], hc[h], false);
+    v.push_back({p + "2.weight", (int64_t)ho[h] * hc[h]});
+    v.push_back({p + "2.bias", ho[h]});
+  }
+  return v;
+}
+
+int tensor_index(const char* name) {
+  static std::map<std::string, int> idx;
+  if (idx.empty()) {
+    const auto& r = registry();
+    for (size_t i = 0; i < r.size(); ++i) idx[r[i].name] = (int)i;
+  }
+  auto it = idx.find(name);
+  return it == idx.end() ? -1 : it->second;
+}
+
+float* upload(umt_model* m, const std::vector<float>& v) {
+  float* d = nullptr;
+  if (cudaMalloc(&d, v.size() * sizeof(float)) != cudaSuccess) {
+    fail(UMT_ERR_CUDA, "cudaMalloc of %zu bytes failed", v.size() * sizeof(float));
+    return nullptr;
+  }
+  m->owned.push_back(d);
+  if (cudaMemcpy(d, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) {
+    fail(UMT_ERR_CUDA, "weight upload failed");
+    return nullptr;
+  }
+  return d;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+}  // namespace umt
+
+using namespace umt;
+
+extern "C" const char* umt_last_error(void) { return last_error_buffer(); }
+extern "C" int umt_abi_version(void) { return 1; }
+extern "C" int umt_model_num_tensors(void) { return (int)registry().size(); }
+extern "C" const char* umt_model_tensor_name(int i) {
+  const auto& r = registry();
+  return (i >= 0 && i < (int)r.size()) ? r[i].name.c_str() : nullptr;
+}
+extern "C" int64_t umt_model_tensor_numel(int i) {
+  const auto& r = registry();
+  return (i >= 0 && i < (int)r.size()) ? r[i].numel : -1;
+}
+
+extern "C" int umt_model_create(const float* const* host_tensors, int n_tensors, umt_model** out) {
+  if (!out) return fail(UMT_ERR_INVALID, "umt_model_create: out is null");
+  *out = nullptr;
+  if (!host_tensors || n_tensors != (int)registry().size())
+    return fail(UMT_ERR_INVALID, "umt_model_create: expected %d tensors, got %d",
+                (int)registry().size(), n_tensors);
+  for (int i = 0; i < n_tensors; ++i)
+    if (!host_tensors[i])
+      return fail(UMT_ERR_INVALID, "umt_model_create: tensor %d (%s) is null", i, registry()[i].name.c_str());
+  int dev = 0, major = 0;
+  UMT_CUDA_TRY(cudaGetDevice(&dev));
+  UMT_CUDA_TRY(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10)
+    return fail(UMT_ERR_UNSUPPORTED, "umetrack_b200 needs an sm_100 GPU (tcgen05); device %d is sm_%d", dev, major * 10);
+  umt_model* m = new umt_model();
+  int rc = encoder_build(m, host_tensors);
+  if (rc == UMT_OK) rc = tail_build(m, host_tensors);
+  if (rc != UMT_OK) {
+    umt_model_destroy(m);
+    return rc;
+  }
+  *out = m;
+  return UMT_OK;
+}
+
+extern "C" void umt_model_destroy(umt_model* m) {
+  if (!m) return;
+  for (void* p : m->owned) cudaFree(p);
+  delete m;
+}
+
+static size_t tail_bytes(int max_images, int max_samples, size_t* feats_off, size_t* a_off,
+                         size_t* b_off, size_t* c_off, size_t* s_off) {
+  size_t o = 0;
+  *feats_off = o; o += align256((size_t)max_images * 72 * 36 * 4);
+  *a_off = o; o += align256((size_t)max_samples * 144 * 36 * 4);
+  *b_off = o; o += align256((size_t)max_samples * 144 * 36 * 4);
+  *c_off = o; o += align256((size_t)max_samples * 144 * 36 * 4);
+  *s_off = o; o += align256((size_t)max_samples * 4 * 36 * 4);
+  return o;
+}
+
+extern "C" int umt_model_workspace_bytes(const umt_model* m, int chunk_images, int max_images,
+                                         int max_samples, size_t* bytes) {
+  if (!m || !bytes || chunk_images < 1 || max_images <= 0 || max_samples <= 0)
+    return fail(UMT_ERR_INVALID, "umt_model_workspace_bytes: bad arguments");
+  size_t f, a, b, c, s;
+  *bytes = encoder_workspace_bytes(chunk_images) + tail_bytes(max_images, max_samples, &f, &a, &b, &c, &s);
+  return UMT_OK;
+}
+
+extern "C" int umt_model_bind_workspace(umt_model* m, void* workspace, size_t bytes, int chunk_images,
+                                        int max_images, int max_samples, void* stream) {
+  if (!m || !workspace) return fail(UMT_ERR_INVALID, "umt_model_bind_workspace: null argument");
+  size_t need = 0;
+  UMT_TRY(umt_model_workspace_bytes(m, chunk_images, max_images, max_samples, &need));
+  if (bytes < need)
+    return fail(UMT_ERR_INVALID, "umt_model_bind_workspace: %zu bytes given, %zu needed", bytes, need);
+  if (((uintptr_t)workspace & 255) != 0)
+    return fail(UMT_ERR_INVALID, "umt_model_bind_workspace: workspace must be 256-byte aligned");
+  // halo rows of the activation tensors must read as zero for the whole life of the binding
+  UMT_CUDA_TRY(cudaMemsetAsync(workspace, 0, need, (cudaStream_t)stream));
+  m->ws = (uint8_t*)workspace;
+  m->chunk_images = chunk_images;
+  m->ws_bytes = bytes;
+  m->ws_max_images = max_images;
+  m->ws_max_samples = max_samples;
+  encoder_bind(m, m->ws);
+  size_t f, a, b, c, s;
+  tail_bytes(max_images, max_samples, &f, &a, &b, &c, &s);
+  uint8_t* t = m->ws + encoder_workspace_bytes(chunk_images);
+  m->feats = (float*)(t + f);
+  m->tail_a = (float*)(t + a);
+  m->tail_b = (float*)(t + b);
+  m->tail_c = (float*)(t + c);
+  m->tail_skel = (float*)(t + s);
+  return UMT_OK;
+}
+
+static int encode_all(umt_model* m, int mode, const float* images, int n_img, float* features,
+                      cudaStream_t st) {
+  for (int i0 = 0; i0 < n_img; i0 += m->chunk_images) {
+    const int n = (n_img - i0 < m->chunk_images) ? n_img - i0 : m->chunk_images;
+    UMT_TRY(encoder_run_chunk(m, mode, images + (size_t)i0 * 9216, n, features + (size_t)i0 * 72 * 36, -1, st));
+  }
+  return UMT_OK;
+}
+
+extern "C" int umt_model_encode(umt_model* m, int mode, const float* images, int n_img,
+                                float* features, void* stream) {
+  if (!m || !images || !features) return fail(UMT_ERR_INVALID, "umt_model_encode: null argument");
+  if (mode != UMT_MODE_FP32_EQUIV && mode != UMT_MODE_BF16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
+  if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_encode: no workspace bound");
+  if (n_img < 0) return fail(UMT_ERR_INVALID, "umt_model_encode: n_img=%d", n_img);
+  m->launches = 0;
+  if (n_img == 0) return UMT_OK;
+  return encode_all(m, mode, images, n_img, features, (cudaStream_t)stream);
+}
+
+extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* images,
+                                 const float* intrinsics, const float* extrinsics,
+                                 const int64_t* sample_range, const int64_t* memory_idx,
+                                 const uint8_t* use_memory, const int64_t* hand_idx, int n_img,
+                                 int n_samples, const float* skel_axes, const float* skel_rest,
+                                 int n_skel, float* mem_state, float* prev_extr, int n_slots,
+                                 float* out_joint_angles, float* out_wrist, float* out_scale,
+                                 float* out_sigma, void* stream) {
+  if (!m) return fail(UMT_ERR_INVALID, "umt_model_forward: model is null");
+  if (mode != UMT_MODE_FP32_EQUIV && mode != UMT_MODE_BF16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
+  if (head != UMT_HEAD_KNOWN_SKELETON && head != UMT_HEAD_UNKNOWN_SKELETON)
+    return fail(UMT_ERR_INVALID, "bad head %d", head);
+  if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_forward: no workspace bound");
+  if (n_img <= 0 || n_samples <= 0 || n_img > m->ws_max_images || n_samples > m->ws_max_samples)
+    return fail(UMT_ERR_INVALID, "umt_model_forward: n_img=%d n_samples=%d exceed the bound workspace (%d, %d)",
+                n_img, n_samples, m->ws_max_images, m->ws_max_samples);
+  if (!images || !intrinsics || !extrinsics || !sample_range || !memory_idx || !use_memory ||
+      !hand_idx || !mem_state || !prev_extr || !out_joint_angles || !out_wrist || !out_sigma)
+    return fail(UMT_ERR_INVALID, "umt_model_forward: null pointer argument");
+  if (head == UMT_HEAD_KNOWN_SKELETON) {
+    if (!skel_axes || !skel_rest || !(n_skel == 1 || n_skel == n_samples))
+      return fail(UMT_ERR_INVALID, "umt_model_forward: known-skeleton head needs 1 or n_samples skeletons");
+  } else if (!out_scale) {
+    return fail(UMT_ERR_INVALID, "umt_model_forward: unknown-skeleton head needs out_scale");
+  }
+  if (n_slots <= 0) return fail(UMT_ERR_INVALID, "umt_model_forward: n_slots=%d", n_slots);
+  cudaStream_t st = (cudaStream_t)stream;
+  m->launches = 0;
+  UMT_TRY(encode_all(m, mode, images, n_img, m->feats, st));
+  return tail_forward(m, head, m->feats, intrinsics, extrinsics, sample_range, memory_idx, use_memory,
+                      hand_idx, n_img, n_samples, skel_axes, skel_rest, n_skel, mem_state, prev_extr,
+                      n_slots, out_joint_angles, out_wrist, out_scale, out_sigma, st);
+}
+
+extern "C" int umt_model_last_launch_count(const umt_model* m) { return m ? m->launches : 0; }
+
+extern "C" int umt_model_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
+                                     float* out_simt, float* out_umma, int* out_shape, void* stream) {
+  if (!m || !images) return fail(UMT_ERR_INVALID, "umt_model_debug_layer: null argument");
+  if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_debug_layer: no workspace bound");
+  return encoder_debug_layer(m, mode, layer, images, n_img, out_simt, out_umma, out_shape,
+                             (cudaStream_t)stream);
+}
+
+extern "C" int umt_model_profile_layers(umt_model* m, int mode, const float* images, int n_img,
+                                        float* out_ms, void* stream) {
+  if (!m || !images || !out_ms) return fail(UMT_ERR_INVALID, "umt_model_profile_layers: null argument");
+  if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_profile_layers: no workspace bound");
+  if (n_img <= 0 || n_img > m->chunk_images || n_img > m->ws_max_images)
+    return fail(UMT_ERR_INVALID, "umt_model_profile_layers: n_img=%d must fit one chunk (%d)", n_img, m->chunk_images);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaEvent_t ev[33];
+  for (int i = 0; i < 33; ++i) UMT_CUDA_TRY(cudaEventCreate(&ev[i]));
+  m->launches = 0;
+  int rc = encoder_run_chunk(m, mode, images, n_img, m->feats, -1, st, ev);
+  if (rc == UMT_OK) {
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) rc = fail(UMT_ERR_CUDA, "profile sync: %s", cudaGetErrorString(e));
+  }
+  if (rc == UMT_OK)
+    for (int i = 0; i < 32; ++i) cudaEventElapsedTime(&out_ms[i], ev[i], ev[i + 1]);
+  for (int i = 0; i < 33; ++i) cudaEventDestroy(ev[i]);
+  return rc;
+}

@@ -1,0 +1,123 @@
+// Internal declarations shared by encoder.cu (backbone), tail.cu (fusion / temporal / heads)
+// and model.cu (handle, workspace, C ABI).  Not part of the public interface.
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+namespace umt {
+
+// ----------------------------------------------------------------------------------------------
+// Activation layout of the backbone ("planar flat"):
+//   An activation tensor for N images of H x W pixels and C channels is stored as C/8 planes.
+//   A plane is a 1-D array of 16-byte rows, one row = 8 consecutive bf16 channels of one
+//   position.  Positions enumerate a halo-padded raster: image i owns (H+1)*(W+1) positions,
+//   q = i*(H+1)*(W+1) + y*(W+1) + x, where column x == W and row y == H are halo positions that
+//   always hold zeros.  Because the right halo of one row is the left halo of the next and the
+//   bottom halo row of one image is the top halo of the next, a 3x3 tap (dy,dx) of position q
+//   is position q + dy*(W+1) + dx -- a constant row shift, for every position of every image.
+//   `guard` zero rows precede position 0 and follow the last tile.
+//   Values are split bf16: x ~= hi + lo, the lo planes live `lo_offset` bytes after the hi
+//   planes (UMT_MODE_BF16 reads and writes only hi).
+// ----------------------------------------------------------------------------------------------
+struct FlatTensor {
+  uint8_t* base;            // hi plane 0, first guard row
+  long long plane_stride;   // bytes between planes
+  long long lo_offset;      // bytes from a hi plane to the matching lo plane
+  int guard;                // guard rows before position 0
+  int pad_;
+};
+
+constexpr int kMaxStages = 40;
+constexpr int kMaxTaps = 16;
+
+struct ConvParams {
+  FlatTensor src[5];
+  FlatTensor out[4];        // [0] for flat output; four parity-phase tensors when phase_out
+  FlatTensor res;           // residual (flat, output geometry); base == nullptr if none
+  const uint8_t* weights;   // packed operand slabs in program order
+  const float* bias;        // [COUT]
+  int H, W;                 // output-domain geometry
+  int n_pos;                // valid positions: n_img * (H+1) * (W+1)
+  int S;                    // 128-row sub-tiles per CTA
+  int lo_shift;             // most negative tap shift (rows)
+  int patch_rows;           // S*128 + hi_shift - lo_shift
+  int n_a, n_b;             // pipeline depths (A patches, B slabs)
+  int n_stages;
+  int phase_out;            // 1: scatter the output into four (H/2, W/2) parity-phase tensors
+  uint8_t st_src[kMaxStages], st_chunk[kMaxStages], st_ntaps[kMaxStages], st_tap0[kMaxStages];
+  short tap_shift[kMaxTaps];
+};
+
+struct ConvLayer {
+  int cout = 0, cin = 0, stride = 1, geom = 0;   // geom: index into {48,24,12,6}
+  int ds_cin = 0;                                 // >0: fused 1x1 stride-2 downsample branch
+  int src_kind = 0;                               // 0: flat buffer, 1: phase tensors
+  int src_buf = 0, out_buf = 0, res_buf = -1;     // buffer ids within the geometry
+  int phase_out = 0;
+  int n_slabs = 0;
+  uint8_t* d_weights = nullptr;                   // packed [slab][hi|lo][2][cout][8] bf16
+  float* d_bias = nullptr;
+  ConvParams prog{};                              // program template (tensors filled per call)
+};
+
+struct TailWeights {
+  // BatchNorm-folded float32 weights, device pointers
+  float *proj_w, *proj_b;                 // [72,256], [72]
+  float *fus_w[3], *fus_b[3];             // 144->108, 108->72, 72->72
+  float *tmp_w[3], *tmp_b[3];             // 90->90 x3
+  float *skel_w, *skel_b;                 // [144,132] with BN(4) folded, [144]
+  float *reg_w[2][4], *reg_b[2][4];       // per head: four 3x3 convs [C,C,3,3] folded
+  float *head_w[2], *head_b[2];           // [n_out, C], [n_out]
+  float *stem_w, *stem_b;                 // [32,9] folded, [32]
+};
+
+struct Geometry {
+  int H, W, C;
+  long long rows;           // rows per plane (guards + padded positions)
+  int guard;
+};
+
+}  // namespace umt
+
+struct umt_model {
+  int chunk_images = 0;
+  std::vector<umt::ConvLayer> convs;      // 30 backbone convolutions in execution order
+  umt::TailWeights tw{};
+  std::vector<void*> owned;               // device allocations to free
+  // workspace binding
+  uint8_t* ws = nullptr;
+  size_t ws_bytes = 0;
+  int ws_max_images = 0, ws_max_samples = 0;
+  umt::Geometry geo[4]{};
+  umt::FlatTensor buf[4][3]{};            // per geometry: ping, pong, mid
+  umt::FlatTensor phase[4][4]{};          // phase[g]: input of geometry g (g=1..3), 4 parities
+  float* feats = nullptr;                 // [max_images,72,36]
+  float* tail_a = nullptr;                // [max_samples,144,36]
+  float* tail_b = nullptr;                // [max_samples,144,36]
+  float* tail_c = nullptr;                // [max_samples,144,36]
+  float* tail_skel = nullptr;             // [max_samples,4,36]
+  int launches = 0;
+};
+
+namespace umt {
+// encoder.cu
+int encoder_build(umt_model* m, const float* const* t);
+int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, float* features,
+                      int stop_after_layer, cudaStream_t st, cudaEvent_t* ev = nullptr);
+int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
+                        float* out_simt, float* out_umma, int* shape, cudaStream_t st);
+size_t encoder_workspace_bytes(int chunk_images);
+void encoder_bind(umt_model* m, uint8_t* base);
+// tail.cu
+int tail_build(umt_model* m, const float* const* t);
+int tail_forward(umt_model* m, int head, const float* feats, const float* intrinsics,
+                 const float* extrinsics, const int64_t* sample_range, const int64_t* memory_idx,
+                 const uint8_t* use_memory, const int64_t* hand_idx, int n_img, int n_samples,
+                 const float* skel_axes, const float* skel_rest, int n_skel, float* mem_state,
+                 float* prev_extr, int n_slots, float* out_joint_angles, float* out_wrist,
+                 float* out_scale, float* out_sigma, cudaStream_t st);
+// model.cu
+int tensor_index(const char* name);   // index into the umt_model_create tensor list, -1 if absent
+float* upload(umt_model* m, const std::vector<float>& v);
+}  // namespace umt

@@ -1,0 +1,113 @@
+"""Recording-level drivers: the per-frame loop of the reference's eval scripts, and sharding of
+recordings across GPUs.
+
+`track_recording` is the body of `_track_sequence` (run_eval_known_skeleton.py:48-102):
+gen_crop_cameras -> track_frame -> landmarks for prediction and ground truth, MPJPE over valid
+hand-frames.  `calibrate_scale` is pass 1 of run_eval_unknown_skeleton.py:49-78.  Recordings
+are supplied as the label dict of lib/tracker/video_pose_data.py:75-93 plus raw uint8 frames
+[T, H, n_cam*W] (video decode is outside the path).
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterator, Optional, Tuple
+
+import numpy as np
+import torch
+
+from .cameras import read_camera_from_json
+from .hand_model import HandModel, NUM_HANDS, NUM_LANDMARKS_PER_HAND, load_hand_model_from_dict, scaled_hand_model
+from .hand_tracker import (HandTracker, HandTrackerOpts, InputFrame, SingleHandPose, ViewData,
+                           landmarks_from_poses)
+from .metrics import MetricSums
+
+
+class RecordingStream:
+    """Iterates (InputFrame, gt_tracking) like SyncedImagePoseStream.__iter__
+    (lib/tracker/video_pose_data.py:106-151)."""
+
+    def __init__(self, labels: dict, frames: np.ndarray):
+        self.cameras = [read_camera_from_json(c) for c in labels["cameras"]]
+        self.camera_angles = labels["camera_angles"]
+        self.hand_model: HandModel = load_hand_model_from_dict(labels["hand_model"])
+        self.joint_angles = np.array(labels["joint_angles"])
+        self.wrist_transforms = np.array(labels["wrist_transforms"])
+        self.hand_confidences = np.array(labels["hand_confidences"])
+        self.camera_to_world = np.array(labels["camera_to_world_transforms"])
+        self.frames = frames
+        assert len(self.joint_angles) == len(frames)
+
+    def __len__(self):
+        return len(self.frames)
+
+    def __iter__(self) -> Iterator[Tuple[InputFrame, Dict[int, SingleHandPose]]]:
+        n_cam = len(self.cameras)
+        for t, raw in enumerate(self.frames):
+            gt = {}
+            for h in range(2):
+                if self.hand_confidences[t, h] > 0:
+                    gt[h] = SingleHandPose(self.joint_angles[t, h], self.wrist_transforms[t, h],
+                                           self.hand_confidences[t, h])
+            mv = raw.reshape(raw.shape[0], n_cam, -1)
+            if self.camera_to_world[t].sum() == 0:
+                assert not gt, "Cameras are not tracked, expecting no ground truth tracking!"
+            views = [ViewData(image=mv[:, c, :], camera=self.cameras[c].copy(camera_to_world_xf=self.camera_to_world[t, c]),
+                              camera_angle=self.camera_angles[c]) for c in range(n_cam)]
+            yield InputFrame(views=views), gt
+
+
+def track_recording(model, labels: dict, frames: np.ndarray, hand_model: Optional[HandModel] = None,
+                    sums: Optional[MetricSums] = None):
+    """Known-skeleton tracking of one recording.  Returns dict with tracked_keypoints,
+    gt_keypoints [2,T,21,3] (float64, mm), valid_tracking [2,T] and per_frame_mean_error --
+    the same arrays the reference pickles (run_eval_known_skeleton.py:92-100)."""
+    stream = RecordingStream(labels, frames)
+    T = len(stream)
+    pred_model = stream.hand_model if hand_model is None else hand_model
+    tracked = np.zeros([NUM_HANDS, T, NUM_LANDMARKS_PER_HAND, 3])
+    gtk = np.zeros([NUM_HANDS, T, NUM_LANDMARKS_PER_HAND, 3])
+    valid = np.zeros([NUM_HANDS, T], dtype=bool)
+    tracker = HandTracker(model, HandTrackerOpts())
+    for t, (frame, gt) in enumerate(stream):
+        cc = tracker.gen_crop_cameras([v.camera for v in frame.views], stream.camera_angles,
+                                      pred_model, gt, min_num_crops=1)
+        res = tracker.track_frame(frame, pred_model, cc)
+        hands = sorted(res.hand_poses.keys())
+        if not hands:
+            continue
+        ja = np.stack([res.hand_poses[h].joint_angles for h in hands] + [gt[h].joint_angles for h in hands])
+        wr = np.stack([res.hand_poses[h].wrist_xform for h in hands] + [gt[h].wrist_xform for h in hands])
+        n = len(hands)
+        lm_pred = landmarks_from_poses(pred_model, ja[:n], wr[:n], hands)
+        lm_gt = landmarks_from_poses(stream.hand_model, ja[n:], wr[n:], hands)
+        for k, h in enumerate(hands):
+            tracked[h, t], gtk[h, t], valid[h, t] = lm_pred[k], lm_gt[k], True
+    err = np.linalg.norm((gtk - tracked)[valid], axis=-1).mean(axis=-1)
+    if sums is not None:
+        dev = sums.device
+        p = torch.from_numpy(tracked.reshape(-1, 21, 3)).float().to(dev)
+        g = torch.from_numpy(gtk.reshape(-1, 21, 3)).float().to(dev)
+        v = torch.from_numpy(valid.reshape(-1)).to(dev)
+        sums.add_errors(p, g, v)
+        sums.add_accelerations(p.reshape(2, T, 21, 3), v.reshape(2, T), gt=False)
+        sums.add_accelerations(g.reshape(2, T, 21, 3), v.reshape(2, T), gt=True)
+    return {"tracked_keypoints": tracked, "gt_keypoints": gtk, "valid_tracking": valid,
+            "per_frame_mean_error": err}
+
+
+def calibrate_scale(model, labels: dict, frames: np.ndarray, generic_hand_model: HandModel,
+                    n_calibration_samples: int = 30):
+    """Pass 1 of the unknown-skeleton eval: mean predicted scale over the first
+    `n_calibration_samples` two-view hand-frames -> scaled generic hand model."""
+    stream = RecordingStream(labels, frames)
+    tracker = HandTracker(model, HandTrackerOpts())
+    scales = []
+    for frame, gt in stream:
+        cc = tracker.gen_crop_cameras([v.camera for v in frame.views], stream.camera_angles,
+                                      generic_hand_model, gt, min_num_crops=2)
+        res = tracker.track_frame_and_calibrate_scale(frame, cc)
+        for h in res.hand_poses.keys():
+            scales.append(res.predicted_scales[h])
+        if len(scales) >= n_calibration_samples:
+            break
+    mean_scale = float(np.mean(scales)) if scales else 1.0
+    return scaled_hand_model(generic_hand_model, mean_scale), mean_scale, np.array(scales)

@@ -1,0 +1,249 @@
+"""Per-frame tracker: the reference's `HandTracker` API with the three stages on the GPU.
+
+Names and behaviour follow lib/tracker/tracker.py:33-291, lib/tracker/perspective_crop.py:19-162
+and lib/tracker/tracking_result.py:14-30: tracker I/O is in millimetres, model I/O in metres;
+the model predicts left hands, right-hand crops are x-mirrored by the crop camera and the
+result un-mirrored; an empty `crop_cameras` resets the history and returns an empty result.
+
+What runs where: crop-camera selection (a few landmarks, float64) stays on the host; the
+landmark FK it needs, the crop resampling (`_warp_image`), the network and the result FK run
+in libumetrack_b200.so.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, NamedTuple, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import native
+from .cameras import CameraModel, PinholePlaneCameraModel, resample_params
+from .crop_camera import gen_crop_parameters_from_points
+from .hand_model import HandModel, NUM_HANDS, NUM_JOINTS_PER_HAND, RIGHT_HAND_INDEX, scaled_hand_model
+from .model import InputFrameData, InputFrameDesc, InputSkeletonData, RegressorOutput
+from .skinning import fk_landmarks_device
+
+MM_TO_M = 0.001
+M_TO_MM = 1000.0
+CONFIDENCE_THRESHOLD = 0.5
+MAX_VIEW_NUM = 2
+
+
+class SingleHandPose(NamedTuple):
+    """joint angles (22 DoF) + root-to-world wrist transform (mm)."""
+
+    joint_angles: np.ndarray = np.zeros(NUM_JOINTS_PER_HAND, dtype=np.float32)
+    wrist_xform: np.ndarray = np.eye(4, dtype=np.float32)
+    hand_confidence: float = 1.0
+
+
+class TrackingResult(NamedTuple):
+    hand_poses: Dict[int, SingleHandPose] = {}
+    num_views: Dict[int, int] = {}
+    predicted_scales: Dict[int, float] = {}
+
+
+@dataclass
+class ViewData:
+    image: np.ndarray
+    camera: CameraModel
+    camera_angle: float
+
+
+@dataclass
+class InputFrame:
+    views: List[ViewData]
+
+
+@dataclass
+class HandTrackerOpts:
+    num_crop_points: int = 63
+    enable_memory: bool = True
+    use_stored_pose_for_crop: bool = True
+    hand_ratio_in_crop: float = 0.95
+    min_required_vis_landmarks: int = 19
+
+
+def neutral_joint_angles(hand_model: HandModel, lower_factor: float = 0.5) -> torch.Tensor:
+    lim = hand_model.joint_limits
+    assert lim is not None
+    return lim[..., 0] * lower_factor + lim[..., 1] * (1 - lower_factor)
+
+
+def landmarks_from_poses(hand_model: HandModel, joint_angles: np.ndarray, wrists: np.ndarray,
+                         hand_indices) -> np.ndarray:
+    """Batched `landmarks_from_hand_pose`: [n,22], [n,4,4], n hand indices -> [n,21,3] (host)."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    ja = torch.from_numpy(np.ascontiguousarray(joint_angles, dtype=np.float32)).to(dev)
+    wr = torch.from_numpy(np.ascontiguousarray(wrists, dtype=np.float32)).to(dev)
+    mirror = torch.tensor([1 if h == RIGHT_HAND_INDEX else 0 for h in hand_indices], dtype=torch.uint8, device=dev)
+    return fk_landmarks_device(hand_model, ja, wr, mirror).cpu().numpy()
+
+
+def landmarks_from_hand_pose(hand_model: HandModel, hand_pose: SingleHandPose, hand_idx: int) -> np.ndarray:
+    """World-space landmarks [21,3] of one pose (lib/tracker/perspective_crop.py:40-51)."""
+    return landmarks_from_poses(hand_model, np.asarray(hand_pose.joint_angles)[None],
+                                np.asarray(hand_pose.wrist_xform)[None], [hand_idx])[0]
+
+
+def _visible_count(cam: CameraModel, pts_world: np.ndarray) -> int:
+    eye = cam.world_to_eye(pts_world)
+    win = cam.eye_to_window(eye)
+    ok = ((win[..., 0] >= 0) & (win[..., 0] <= cam.width - 1) & (win[..., 1] >= 0)
+          & (win[..., 1] <= cam.height - 1) & (eye[..., 2] > 0))
+    return int(ok.sum())
+
+
+def gen_crop_cameras_from_pose(cameras, camera_angles, hand_model: HandModel, hand_pose: SingleHandPose,
+                               hand_idx: int, num_crop_points: int, new_image_size,
+                               max_view_num: Optional[int] = None, sort_camera_index: bool = False,
+                               focal_multiplier: float = 0.95, mirror_right_hand: bool = True,
+                               min_required_vis_landmarks: int = 19) -> Dict[int, PinholePlaneCameraModel]:
+    """Crop cameras for one hand (lib/tracker/perspective_crop.py:54-162): crop points are the
+    landmarks of the given, the neutral and the open pose (one FK launch for all three);
+    cameras seeing at least `min_required_vis_landmarks` landmarks are eligible, ranked by
+    visibility (or by index when `sort_camera_index`), at most `max_view_num` are used."""
+    assert num_crop_points in (21, 42, 63)
+    n_pose = num_crop_points // 21
+    ja = np.zeros((3, NUM_JOINTS_PER_HAND), dtype=np.float32)
+    ja[0] = np.asarray(hand_pose.joint_angles, dtype=np.float32)
+    ja[1] = neutral_joint_angles(hand_model).numpy()
+    wr = np.repeat(np.asarray(hand_pose.wrist_xform)[None], 3, axis=0)
+    lms = landmarks_from_poses(hand_model, ja[:n_pose], wr[:n_pose], [hand_idx] * n_pose)
+    crop_points = lms.reshape(-1, 3)
+    counts = [_visible_count(c, lms[0]) for c in cameras]
+    eligible = [i for i, n in enumerate(counts) if n >= min_required_vis_landmarks]
+    eligible.sort(reverse=True, key=lambda i: counts[i])
+    if sort_camera_index:
+        eligible = sorted(eligible)
+    out: Dict[int, PinholePlaneCameraModel] = {}
+    for cam_idx in eligible:
+        out[cam_idx] = gen_crop_parameters_from_points(
+            cameras[cam_idx], crop_points, new_image_size,
+            mirror_img_x=(mirror_right_hand and hand_idx == 1),
+            camera_angle=camera_angles[cam_idx], focal_multiplier=focal_multiplier)
+        if len(out) == max_view_num:
+            break
+    return out
+
+
+def warp_views_device(views: List[ViewData], pairs: List[Tuple[int, PinholePlaneCameraModel]],
+                      device: torch.device, want_u8: bool = False):
+    """GPU `_warp_image` for a list of (view index, crop camera) pairs of one frame: returns the
+    float32 crops [n,96,96] in [0,1] (and the uint8 crops if asked) on `device`."""
+    used = sorted({v for v, _ in pairs})
+    slot = {v: k for k, v in enumerate(used)}
+    h, w = views[used[0]].image.shape
+    stack = np.empty((len(used), h, w), dtype=np.uint8)
+    for v in used:
+        if views[v].image.shape != (h, w):
+            raise ValueError("all views of a frame must have the same size")
+        stack[slot[v]] = views[v].image
+    src = torch.from_numpy(stack).to(device)
+    params = torch.from_numpy(np.stack([resample_params(views[v].camera, cam) for v, cam in pairs])).to(device)
+    offsets = torch.tensor([slot[v] * h * w for v, _ in pairs], dtype=torch.int64, device=device)
+    n = len(pairs)
+    out_f = torch.empty((n, 96, 96), dtype=torch.float32, device=device)
+    out_u = torch.empty((n, 96, 96), dtype=torch.uint8, device=device) if want_u8 else None
+    with torch.cuda.device(device):
+        native.check(native.lib().umt_resample_crops(
+            native.ptr(src), native.ptr(offsets), w, w, h, native.ptr(params), n, native.ptr(out_u),
+            native.ptr(out_f), 0, native.current_stream_ptr()), "umt_resample_crops")
+    return (out_f, out_u) if want_u8 else out_f
+
+
+class HandTracker:
+    def __init__(self, model, opts: HandTrackerOpts) -> None:
+        if not torch.cuda.device_count():
+            raise native.NativeError("HandTracker: no CUDA device (this implementation is GPU only)")
+        self._device = torch.device("cuda", torch.cuda.current_device())
+        self._model = model
+        self._model.to(self._device)
+        self._input_size = np.array(self._model.getInputImageSizes())
+        self._num_crop_points = opts.num_crop_points
+        self._enable_memory = opts.enable_memory
+        self._hand_ratio_in_crop = opts.hand_ratio_in_crop
+        self._min_required_vis_landmarks = opts.min_required_vis_landmarks
+        self._valid_tracking_history = np.zeros(2, dtype=bool)
+
+    def reset_history(self) -> None:
+        self._valid_tracking_history[:] = False
+
+    def gen_crop_cameras(self, cameras, camera_angles, hand_model: HandModel,
+                         gt_tracking: Dict[int, SingleHandPose], min_num_crops: int):
+        out: Dict[int, Dict[int, PinholePlaneCameraModel]] = {}
+        for hand_idx, pose in (gt_tracking or {}).items():
+            if pose.hand_confidence < CONFIDENCE_THRESHOLD:
+                continue
+            per_hand = gen_crop_cameras_from_pose(
+                cameras, camera_angles, hand_model, pose, hand_idx, self._num_crop_points,
+                self._input_size, max_view_num=MAX_VIEW_NUM, sort_camera_index=True,
+                focal_multiplier=self._hand_ratio_in_crop, mirror_right_hand=True,
+                min_required_vis_landmarks=self._min_required_vis_landmarks)
+            if per_hand and len(per_hand) >= min_num_crops:
+                out[hand_idx] = per_hand
+        return out
+
+    def track_frame(self, sample: InputFrame, hand_model: HandModel, crop_cameras) -> TrackingResult:
+        if not crop_cameras:
+            self.reset_history()
+            return TrackingResult()
+        data, desc, skel = self._make_inputs(sample, hand_model, crop_cameras)
+        out = self._model.regress_pose_use_skeleton(data, desc, skel)
+        return self._gen_tracking_result(out, desc.hand_idx.cpu().numpy(), crop_cameras)
+
+    def track_frame_and_calibrate_scale(self, sample: InputFrame, crop_cameras) -> TrackingResult:
+        if not crop_cameras:
+            self.reset_history()
+            return TrackingResult()
+        data, desc, _ = self._make_inputs(sample, None, crop_cameras)
+        out = self._model.regress_pose_pred_skel_scale(data, desc)
+        return self._gen_tracking_result(out, desc.hand_idx.cpu().numpy(), crop_cameras)
+
+    def _make_inputs(self, sample: InputFrame, hand_model_mm: Optional[HandModel], crop_cameras):
+        pairs, intr, extr, ranges, hands = [], [], [], [], []
+        for hand_idx, per_hand in crop_cameras.items():
+            start = len(pairs)
+            for cam_idx, crop_cam in per_hand.items():
+                pairs.append((cam_idx, crop_cam))
+                intr.append(crop_cam.uv_to_window_matrix())
+                w2e = np.linalg.inv(crop_cam.camera_to_world_xf)
+                w2e[:3, 3] *= MM_TO_M
+                extr.append(w2e)
+            if len(pairs) > start:
+                hands.append(hand_idx)
+                ranges.append([start, len(pairs)])
+        hands_np = np.array(hands)
+        dev = self._device
+        data = InputFrameData(
+            left_images=warp_views_device(sample.views, pairs, dev),
+            intrinsics=torch.from_numpy(np.stack(intr)).float().to(dev),
+            extrinsics_xf=torch.from_numpy(np.stack(extr)).float().to(dev))
+        desc = InputFrameDesc(
+            sample_range=torch.tensor(ranges, dtype=torch.int64, device=dev),
+            memory_idx=torch.from_numpy(hands_np).long().to(dev),
+            use_memory=torch.from_numpy(self._valid_tracking_history[hands_np]).bool().to(dev),
+            hand_idx=torch.from_numpy(hands_np).long().to(dev))
+        skel = None
+        if hand_model_mm is not None:
+            hm = scaled_hand_model(hand_model_mm, MM_TO_M)
+            skel = InputSkeletonData(joint_rotation_axes=hm.joint_rotation_axes.float().to(dev),
+                                     joint_rest_positions=hm.joint_rest_positions.float().to(dev))
+        return data, desc, skel
+
+    def _gen_tracking_result(self, out: RegressorOutput, hand_indices: np.ndarray, crop_cameras) -> TrackingResult:
+        ja = out.joint_angles.to("cpu").numpy()
+        wr = out.wrist_xfs.to("cpu").numpy()
+        wr[..., :3, 3] *= M_TO_MM
+        scales = None if out.skel_scales is None else out.skel_scales.to("cpu").numpy()
+        poses, n_views, pred_scales = {}, {}, {}
+        for i, h in enumerate(hand_indices):
+            h = int(h)
+            poses[h] = SingleHandPose(joint_angles=ja[i], wrist_xform=wr[i], hand_confidence=1.0)
+            n_views[h] = len(crop_cameras[h])
+            if scales is not None:
+                pred_scales[h] = scales[i]
+        for h in range(NUM_HANDS):
+            self._valid_tracking_history[h] = h in poses
+        return TrackingResult(hand_poses=poses, num_views=n_views, predicted_scales=pred_scales)
