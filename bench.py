@@ -29,7 +29,7 @@ CPU_SAMPLE_BATCH = 160  # the reference script's batch size (run_inference_torch
 
 
 def conv_flops_per_crop():
-    """Algorithmic FLOPs (2*MAC) of each of the 30 backbone convolutions for one crop, in
+    """Algorithmic FLOPs (2*MAC) of each of the 24 backbone convolutions for one crop, in
     execution order (downsample branch counted with the conv2 it is fused into)."""
     from umetrack_b200 import arch
 
@@ -285,7 +285,7 @@ def main():
     }
 
     if rank == 0:
-        # ---- roofline of the dominant kernel family: the 30 tcgen05 convolutions ----
+        # ---- roofline of the dominant kernel family: the 24 tcgen05 convolutions ----
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -295,25 +295,25 @@ def main():
         peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if peaks else "fallback 1.4 PFLOP/s sustained"
         n_prof = min(d["left_images"].shape[0], 2048)
         reps = 3
-        acc = np.zeros(32)
+        acc = np.zeros(26)
         model.profile_layers(d["left_images"][:n_prof])
         for _ in range(reps):
             acc += np.array(model.profile_layers(d["left_images"][:n_prof]))
         acc /= reps
         flops = np.array(conv_flops_per_crop(), dtype=np.float64) * n_prof
-        conv_ms = acc[1:31]
+        conv_ms = acc[1:25]
         achieved = flops.sum() / (conv_ms.sum() * 1e-3) / 1e12
         executed = achieved * (3 if args.mode == "fp32" else 1)
         line["roofline"] = {
             "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
             "frac": achieved / peak_tf, "traffic": None,
-            "kernel": "conv_umma_kernel (30 launches per encoder pass)",
+            "kernel": "conv_umma_kernel (24 launches per encoder pass)",
             "peak_source": peak_src,
-            "note": "achieved = algorithmic conv FLOPs / sum of the 30 launch durations (CUDA events inside "
+            "note": "achieved = algorithmic conv FLOPs / sum of the 24 launch durations (CUDA events inside "
                     "umt_model_profile_layers); the fp32-equivalent mode executes 3 tensor-core products per "
                     "algorithmic MAC",
             "executed_tensor_tflops": executed, "executed_frac": executed / peak_tf,
-            "conv_ms_per_pass": float(conv_ms.sum()), "stem_ms": float(acc[0]), "proj_ms": float(acc[31]),
+            "conv_ms_per_pass": float(conv_ms.sum()), "stem_ms": float(acc[0]), "proj_ms": float(acc[25]),
             "crops_per_pass": n_prof,
             "per_layer_tflops": [float(f / (t * 1e-3) / 1e12) for f, t in zip(flops, conv_ms)],
         }

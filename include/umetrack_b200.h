@@ -130,12 +130,12 @@ int umt_model_encode(umt_model* m, int mode, const float* images, int n_img, flo
 int umt_model_last_launch_count(const umt_model* m);
 
 /* Measurement hook: one encoder pass over n_img crops (one chunk) with a CUDA event between
- * consecutive launches; out_ms is a HOST float[32]: stem, the 30 convolutions in execution order,
+ * consecutive launches; out_ms is a HOST float[26]: stem, the 24 convolutions in execution order,
  * projection.  Synchronises the stream (this is the only entry point that does). */
 int umt_model_profile_layers(umt_model* m, int mode, const float* images, int n_img, float* out_ms,
                              void* stream);
 
-/* Test hook: run the encoder on `images` [n_img,96,96] up to convolution `layer` (0..29,
+/* Test hook: run the encoder on `images` [n_img,96,96] up to convolution `layer` (0..23,
  * execution order), then evaluate that layer twice on the same inputs: with plain CUDA-core
  * arithmetic into out_simt and with the tensor-core kernel into out_umma, both as dense float32
  * [n_img, C, H, W] (no halo), so the tensor-core path can be checked layer by layer.  Either

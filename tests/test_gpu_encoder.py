@@ -30,7 +30,7 @@ def setup():
     return sd, model, imgs, taps, feats
 
 
-@pytest.mark.parametrize("layer", list(range(30)))
+@pytest.mark.parametrize("layer", list(range(24)))
 def test_each_conv_tensor_core_vs_cuda_core_and_oracle(setup, layer):
     sd, model, imgs, taps, _ = setup
     simt, umma = model.debug_layer(layer, imgs)
@@ -54,7 +54,7 @@ def test_backbone_features_vs_reference_golden(setup):
     b = synthetic.make_model_batch(6, seed=100, single_view_every=3)
     got = model.encode(b["left_images"][:3]).cpu().numpy()
     assert np.abs(got - g).max() <= 3e-4 * np.abs(g).max()
-    assert model.last_launch_count == 32   # stem + 30 convs + projection
+    assert model.last_launch_count == 26   # stem + 24 convs + projection
 
 
 def test_chunking_and_batch_independence(setup):

@@ -24,7 +24,7 @@ model = UmeTrackModel(sd).to("cuda")
 bad = False
 for mode in ("fp32", "bf16"):
     model.set_mode(mode)
-    for layer in range(30):
+    for layer in range(24):
         simt, umma = model.debug_layer(layer, imgs)
         torch.cuda.synchronize()
         simt, umma = simt.cpu(), umma.cpu()

@@ -1,4 +1,5 @@
-// Stage (b), part 1: the per-view CNN encoder (30 convolutions, 99 % of the FLOPs) as
+// Stage (b), part 1: the per-view CNN encoder (24 3x3 convolutions with 3 fused 1x1 downsample
+// branches, 99 % of the FLOPs) as
 // implicit-GEMM convolutions on the 5th-generation tensor cores (tcgen05.mma, accumulators in
 // TMEM), plus the stem (conv 1->32 + BN + ReLU + 2x2 max-pool) and the 256->72 projection on CUDA
 // cores.  Reference: lib/models/backbone_resnet.py:14-158, lib/models/model_utils.py:107-138.
@@ -850,7 +851,7 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
     UMT_TRY(launch_conv(p, m->convs[i].cout, split, st));
     ++m->launches;
   }
-  if (ev) cudaEventRecord(ev[31], st);
+  if (ev) cudaEventRecord(ev[1 + m->convs.size()], st);
   if (features) {
     const ConvLayer& last = m->convs.back();
     if (split)
@@ -860,7 +861,7 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
     UMT_TRY(check_launch("proj_kernel"));
     ++m->launches;
   }
-  if (ev) cudaEventRecord(ev[32], st);
+  if (ev) cudaEventRecord(ev[2 + m->convs.size()], st);
   return UMT_OK;
 }
 

@@ -274,8 +274,10 @@ extern "C" int umt_model_profile_layers(umt_model* m, int mode, const float* ima
   if (n_img <= 0 || n_img > m->chunk_images || n_img > m->ws_max_images)
     return fail(UMT_ERR_INVALID, "umt_model_profile_layers: n_img=%d must fit one chunk (%d)", n_img, m->chunk_images);
   cudaStream_t st = (cudaStream_t)stream;
-  cudaEvent_t ev[33];
-  for (int i = 0; i < 33; ++i) UMT_CUDA_TRY(cudaEventCreate(&ev[i]));
+  constexpr int kEv = 27;  // stem, 24 convolutions, projection, end
+  if ((int)m->convs.size() != 24) return fail(UMT_ERR_INVALID, "unexpected layer count");
+  cudaEvent_t ev[kEv];
+  for (int i = 0; i < kEv; ++i) UMT_CUDA_TRY(cudaEventCreate(&ev[i]));
   m->launches = 0;
   int rc = encoder_run_chunk(m, mode, images, n_img, m->feats, -1, st, ev);
   if (rc == UMT_OK) {
@@ -283,7 +285,7 @@ extern "C" int umt_model_profile_layers(umt_model* m, int mode, const float* ima
     if (e != cudaSuccess) rc = fail(UMT_ERR_CUDA, "profile sync: %s", cudaGetErrorString(e));
   }
   if (rc == UMT_OK)
-    for (int i = 0; i < 32; ++i) cudaEventElapsedTime(&out_ms[i], ev[i], ev[i + 1]);
-  for (int i = 0; i < 33; ++i) cudaEventDestroy(ev[i]);
+    for (int i = 0; i < kEv - 1; ++i) cudaEventElapsedTime(&out_ms[i], ev[i], ev[i + 1]);
+  for (int i = 0; i < kEv; ++i) cudaEventDestroy(ev[i]);
   return rc;
 }

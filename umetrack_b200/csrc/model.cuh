@@ -82,7 +82,7 @@ struct Geometry {
 
 struct umt_model {
   int chunk_images = 0;
-  std::vector<umt::ConvLayer> convs;      // 30 backbone convolutions in execution order
+  std::vector<umt::ConvLayer> convs;      // 24 backbone convolutions in execution order
   umt::TailWeights tw{};
   std::vector<void*> owned;               // device allocations to free
   // workspace binding

@@ -284,12 +284,12 @@ class UmeTrackModel:
         return out
 
     def profile_layers(self, images: torch.Tensor):
-        """Per-launch device times (ms) of one encoder pass: [stem, conv0..conv29, projection]."""
+        """Per-launch device times (ms) of one encoder pass: [stem, conv0..conv23, projection]."""
         self._require_handle()
         images = self._prep(images, torch.float32)
         n = images.shape[0]
         self._ensure_workspace(n, 8)
-        out = (ctypes.c_float * 32)()
+        out = (ctypes.c_float * 26)()
         with torch.cuda.device(self._device):
             native.check(native.lib().umt_model_profile_layers(self._handle, self._mode, native.ptr(images), n,
                                                                out, native.current_stream_ptr()),
