@@ -126,6 +126,20 @@ int umt_model_forward(umt_model* m, int mode, int head, const float* images,
 int umt_model_encode(umt_model* m, int mode, const float* images, int n_img, float* features,
                      void* stream);
 
+/* Backbone for callers that cannot allocate device memory.  [No counterpart in the reference,
+ * which is Python and lets torch allocate.]  Same result as umt_model_encode for n_img <= 4
+ * crops (one tracker frame: two hands x two views), but it needs no bound workspace and makes
+ * no device allocation: its scratch is a 13 MiB `static __device__` array inside this library,
+ * resident on every GPU that loads the library until the process exits.  Meant for hosts that
+ * created the model at start-up and later run where cudaMalloc is off limits (frozen memory
+ * budget, a runtime that owns the allocator, a loop that cannot afford cudaMalloc's device-wide
+ * synchronisation).  n_img > 4 returns UMT_ERR_INVALID.  The first call on a device resolves the
+ * array's device address: make it at start-up with that device current and before any stream
+ * capture.  Calls share the one array and clear it first, so calls whose GPU work may overlap
+ * (other streams or threads) race: serialise them. */
+int umt_model_encode_static(umt_model* m, int mode, const float* images, int n_img, float* features,
+                            void* stream);
+
 /* Number of kernels the last umt_model_forward / umt_model_encode call launched. */
 int umt_model_last_launch_count(const umt_model* m);
 

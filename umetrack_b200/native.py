@@ -33,6 +33,7 @@ SIGNATURES = {
     "umt_model_forward": (c_int, [c_void_p, c_int, c_int] + [c_void_p] * 7 + [c_int, c_int, c_void_p,
                                   c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
     "umt_model_encode": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "umt_model_encode_static": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_last_launch_count": (c_int, [c_void_p]),
     "umt_model_profile_layers": (c_int, [c_void_p, c_int, c_void_p, c_int, POINTER(c_float), c_void_p]),
     "umt_model_debug_layer": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p,
