@@ -76,6 +76,16 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
       ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
       : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, %1;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred)
+      : "r"(0xFFFFFFFFu));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -271,71 +281,78 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
                  kBStage, b_full(slot));
       }
     }
-  } else if (warp == 2 && lane == 0) {
-    // ===== MMA issuer =====
+  } else if (warp == 2) {
+    // ===== MMA issuer: the whole warp walks the program (so every value stays warp-uniform and
+    // lives in uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit =====
     constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | (1u << 7) /* A = bf16 */ |
                                (1u << 10) /* B = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
                                ((128u >> 4) << 24);
+    const bool leader = elect_one();
+    const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
+    const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
+    const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)(((COUT * 16u) >> 4) & 0x3FFF) << 16);
     int k = 0;
     uint32_t any = 0;
     for (int i = 0; i < P.n_stages; ++i) {
       const int aslot = i % n_a;
       mbar_wait(a_full(aslot), (uint32_t)(i / n_a) & 1u);
       const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
+      const bool skip_hilo = SPLIT && (P.st_flags[i] & 1);   // identity (residual) slabs have w_lo == 0
       for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
         const int bslot = k % n_b;
         mbar_wait(b_full(bslot), (uint32_t)(k / n_b) & 1u);
         tc_fence_after();
         const uint32_t b_s = smem_u32(b_base + (size_t)bslot * kBStage);
-        const uint64_t b_hi = umma_desc(b_s, COUT * 16u, 128u);
-        const uint64_t b_lo = umma_desc(b_s + kBHalf, COUT * 16u, 128u);
+        const uint64_t b_hi = b_desc_base | (uint64_t)((b_s >> 4) & 0x3FFF);
+        const uint64_t b_lo = b_desc_base | (uint64_t)(((b_s + kBHalf) >> 4) & 0x3FFF);
         const int shift = (int)P.tap_shift[P.st_tap0[i] + t] - P.lo_shift;
-        for (int s = 0; s < P.S; ++s) {
-          const uint32_t a_row = a_s + (uint32_t)(s * 128 + shift) * 16u;
-          const uint64_t a_hi = umma_desc(a_row, a_plane_bytes, 128u);
-          const uint32_t d = tmem_base + (uint32_t)(s * COUT);
-          tc_mma_bf16(d, a_hi, b_hi, idesc, any);
-          if (SPLIT) {
-            const uint64_t a_lo = umma_desc(a_row + 2u * a_plane_bytes, a_plane_bytes, 128u);
-            tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
-            tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
+        const uint32_t a_row0 = a_s + (uint32_t)shift * 16u;
+        if (leader) {
+#pragma unroll 1
+          for (int s = 0; s < P.S; ++s) {
+            const uint32_t a_row = a_row0 + (uint32_t)s * 2048u;
+            const uint64_t a_hi = a_desc_base | (uint64_t)((a_row >> 4) & 0x3FFF);
+            const uint32_t d = tmem_base + (uint32_t)(s * COUT);
+            tc_mma_bf16(d, a_hi, b_hi, idesc, any);
+            if (SPLIT) {
+              const uint64_t a_lo = a_desc_base | (uint64_t)(((a_row + 2u * a_plane_bytes) >> 4) & 0x3FFF);
+              if (!skip_hilo) tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
+              tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
+            }
           }
+          tc_commit(b_empty(bslot));
         }
         any = 1u;
-        tc_commit(b_empty(bslot));
+        __syncwarp();
       }
-      tc_commit(a_empty(aslot));
+      if (leader) tc_commit(a_empty(aslot));
+      __syncwarp();
     }
-    tc_commit(acc_full);
+    if (leader) tc_commit(acc_full);
+    __syncwarp();
   } else if (warp >= 4) {
     // ===== epilogue: TMEM -> registers -> bias / residual / ReLU -> split bf16 -> global =====
     mbar_wait(acc_full, 0u);
     tc_fence_after();
     const int lgrp = warp & 3;  // TMEM lane group this warp may read
-    const bool has_res = P.res.base != nullptr;
     for (int s = 0; s < P.S; ++s) {
       const long long q = q0 + s * 128 + lgrp * 32 + lane;
       const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
       const FlatTensor& T = P.out[o.tensor];
 #pragma unroll 1
-      for (int c0 = 0; c0 < COUT; c0 += 16) {
-        uint32_t v[16];
-        tc_ld16(tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)(s * COUT + c0), v);
+      for (int c0 = 0; c0 < COUT; c0 += 32) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)(s * COUT + c0);
+        tc_ld16(taddr, v);
+        tc_ld16(taddr + 16, v + 16);
         tc_ld_wait();
         if (o.valid) {
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
+          for (int h = 0; h < 4; ++h) {
             float f[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e];
-            if (has_res) {
-              float r[8];
-              load_row8<SPLIT>(P.res, (c0 >> 3) + h, q, r);
-#pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] += r[e];
-            }
-#pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.0f);
+            for (int e = 0; e < 8; ++e)
+              f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], 0.0f);
             store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
           }
         }
@@ -509,7 +526,7 @@ stem_kernel(const float* __restrict__ images, int n_img, const float* __restrict
 // ------------------------------------------------------------------------------------------
 template <bool SPLIT>
 __global__ void __launch_bounds__(432)
-proj_kernel(FlatTensor in, int n_img, const float* __restrict__ w /* [72][256] */,
+proj_kernel(FlatTensor in, int n_img, const float* __restrict__ w /* [256][72], transposed */,
             const float* __restrict__ b, float* __restrict__ out) {
   __shared__ float sx[36][257];
   const int img = blockIdx.x;
@@ -526,9 +543,8 @@ proj_kernel(FlatTensor in, int n_img, const float* __restrict__ w /* [72][256] *
   float acc[6];
 #pragma unroll
   for (int j = 0; j < 6; ++j) acc[j] = b[co];
-  const float* wr = w + (size_t)co * 256;
   for (int ci = 0; ci < 256; ++ci) {
-    const float ww = __ldg(wr + ci);
+    const float ww = __ldg(w + ci * 72 + co);   // consecutive lanes read consecutive channels
 #pragma unroll
     for (int j = 0; j < 6; ++j) acc[j] = fmaf(sx[pg * 6 + j][ci], ww, acc[j]);
   }
@@ -614,6 +630,17 @@ static int env_int(const char* name, int dflt) {
   return s ? atoi(s) : dflt;
 }
 
+// identity slab: adds source channel 16*chunk + k to output channel of the same index
+static void pack_identity_slab(std::vector<uint16_t>& blob, int cout, int chunk) {
+  const size_t base = blob.size();
+  blob.resize(base + (size_t)4 * cout * 8, 0);
+  for (int pl = 0; pl < 2; ++pl)
+    for (int e = 0; e < 8; ++e) {
+      const int co = chunk * 16 + pl * 8 + e;
+      blob[base + ((size_t)pl * cout + co) * 8 + e] = 0x3F80;  // bf16(1.0)
+    }
+}
+
 // Build program + packed weights of one backbone convolution.
 static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds) {
   ConvParams& p = L.prog;
@@ -635,6 +662,17 @@ static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Fold
       ++ns;
       for (int ky = 0; ky < 3; ++ky)
         for (int kx = 0; kx < 3; ++kx) pack_slab(blob, main, c, ky, kx);
+    }
+    if (L.res_buf >= 0) {
+      // identity residual (backbone_resnet.py:66-69): x enters the accumulator as extra K through
+      // identity weight slabs (source 2, centre tap), exactly as hi + lo, instead of being re-read
+      // by the epilogue
+      for (int c = 0; c < L.cout / 16; ++c) {
+        p.st_src[ns] = 2; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = 1; p.st_tap0[ns] = 4;
+        p.st_flags[ns] = 1;
+        ++ns;
+        pack_identity_slab(blob, L.cout, c);
+      }
     }
     if (ds) {  // fused 1x1 stride-2 downsample: source 1 = parity-phase (0,0) of the block input
       for (int c = 0; c < ds->cin / 16; ++c) {
@@ -737,7 +775,10 @@ int encoder_build(umt_model* m, const float* const* t) {
   m->tw.stem_w = upload(m, st.w);
   m->tw.stem_b = upload(m, st.b);
   Folded pj = folded_from(t, "_feature_extractor._image_backbone.1", "", 72, 256, 1, true);
-  m->tw.proj_w = upload(m, pj.w);
+  std::vector<float> pjt((size_t)256 * 72);
+  for (int co = 0; co < 72; ++co)
+    for (int ci = 0; ci < 256; ++ci) pjt[(size_t)ci * 72 + co] = pj.w[(size_t)co * 256 + ci];
+  m->tw.proj_w = upload(m, pjt);
   m->tw.proj_b = upload(m, pj.b);
   if (!m->tw.stem_w || !m->tw.stem_b || !m->tw.proj_w || !m->tw.proj_b) return UMT_ERR_CUDA;
   return UMT_OK;
@@ -811,8 +852,8 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool
   } else {
     p.out[0] = m->buf[g][L.out_buf];
   }
-  if (L.res_buf >= 0) p.res = m->buf[g][L.res_buf];
-  else p.res.base = nullptr;
+  if (L.res_buf >= 0) p.src[2] = m->buf[g][L.res_buf];
+  p.res.base = nullptr;
   p.weights = L.d_weights;
   p.bias = L.d_bias;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);

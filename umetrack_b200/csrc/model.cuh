@@ -34,7 +34,7 @@ constexpr int kMaxTaps = 16;
 struct ConvParams {
   FlatTensor src[5];
   FlatTensor out[4];        // [0] for flat output; four parity-phase tensors when phase_out
-  FlatTensor res;           // residual (flat, output geometry); base == nullptr if none
+  FlatTensor res;           // unused by the tensor-core kernel (residuals enter as identity-weight K)
   const uint8_t* weights;   // packed operand slabs in program order
   const float* bias;        // [COUT]
   int H, W;                 // output-domain geometry
@@ -46,6 +46,7 @@ struct ConvParams {
   int n_stages;
   int phase_out;            // 1: scatter the output into four (H/2, W/2) parity-phase tensors
   uint8_t st_src[kMaxStages], st_chunk[kMaxStages], st_ntaps[kMaxStages], st_tap0[kMaxStages];
+  uint8_t st_flags[kMaxStages];   // bit 0: weight slab has no lo part (identity slab of a residual)
   short tap_shift[kMaxTaps];
 };
 
