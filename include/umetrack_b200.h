@@ -129,7 +129,7 @@ int umt_model_encode(umt_model* m, int mode, const float* images, int n_img, flo
 /* Backbone for callers that cannot allocate device memory.  [No counterpart in the reference,
  * which is Python and lets torch allocate.]  Same result as umt_model_encode for n_img <= 4
  * crops (one tracker frame: two hands x two views), but it needs no bound workspace and makes
- * no device allocation: its scratch is a 13 MiB `static __device__` array inside this library,
+ * no device allocation: its scratch is a 16 MiB `static __device__` array inside this library,
  * resident on every GPU that loads the library until the process exits.  Meant for hosts that
  * created the model at start-up and later run where cudaMalloc is off limits (frozen memory
  * budget, a runtime that owns the allocator, a loop that cannot afford cudaMalloc's device-wide

@@ -2,7 +2,7 @@
 
 A tracker embedded in someone else's runtime, or a per-frame loop running after the application
 froze its GPU memory budget, can still create the model at start-up but cannot cudaMalloc (or let
-torch allocate) a workspace later.  For them the library carries its own 13 MiB scratch array and
+torch allocate) a workspace later.  For them the library carries its own 16 MiB scratch array and
 encodes up to 4 crops (one frame) out of it.  This test drives that entry point through the C ABI
 and requires the same features as the regular, workspace-backed umt_model_encode -- twice in a row,
 because the second call starts from the first call's leftovers in the shared array.
@@ -40,7 +40,7 @@ def test_static_scratch_encode_matches_workspace_encode_twice():
     ref_second = model.encode(second)
     out_first, out_second = _out_like(first), _out_like(second)
     # start-up call, as the header asks: it resolves the array's device address (and lets the
-    # driver load the 13 MiB array), so the calls below are the steady state a real host sees
+    # driver load the 16 MiB array), so the calls below are the steady state a real host sees
     assert _encode_static(model, first[:1].contiguous())[0] == 0
     torch.cuda.synchronize()
     before = (torch.cuda.memory_allocated(dev), torch.cuda.mem_get_info(dev)[0])

@@ -11,8 +11,8 @@
 // and afterwards call this entry point, which performs no device allocation at all: no
 // cudaMalloc/cudaFree, no pool, no torch tensor.
 //
-// The price: the scratch is a 13 MiB `static __device__` array.  Every GPU on which the CUDA
-// runtime loads this part of the library keeps those 13 MiB resident until the process exits
+// The price: the scratch is a 16 MiB `static __device__` array.  Every GPU on which the CUDA
+// runtime loads this part of the library keeps those 16 MiB resident until the process exits
 // (with eager module loading that is every GPU the process touches; with lazy loading, the
 // default since CUDA 12, it is every GPU on which this entry point has been called once -- the
 // driver materialises the array during that first call, which is one more reason to make it at
@@ -37,7 +37,7 @@
 namespace {
 
 constexpr int kStaticMaxCrops = 4;
-constexpr size_t kStaticScratchBytes = 13u << 20;   // >= encoder_workspace_bytes(4) = 12,700,672
+constexpr size_t kStaticScratchBytes = 16u << 20;   // >= encoder_workspace_bytes(4) = 16,174,080
 
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 

@@ -76,6 +76,27 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
       ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
       : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_multicast(uint32_t dst, const void* src, uint32_t bytes,
+                                                   uint32_t bar, uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1], %2, [%3], %4;"
+      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"(cta_mask)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_multicast(uint32_t bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"(cta_mask)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred = 0;
   asm volatile(
@@ -196,6 +217,13 @@ __device__ __forceinline__ OutPos map_output(long long q, int H, int W, int n_po
 // ------------------------------------------------------------------------------------------
 constexpr int kConvThreads = 256;
 
+// Persistent, warp-specialised kernel.  Each CTA (one per SM) walks tiles t = blockIdx.x,
+// blockIdx.x + gridDim.x, ...; a tile is S sub-tiles of 128 positions x all Cout channels.
+// Pipelines: A patches (n_a slots) and weight slabs (n_b slots) keep streaming across tile
+// boundaries; the accumulator lives in n_buf TMEM buffers so the epilogue of tile i overlaps the
+// MMAs of tile i+1.  With a cluster of `cluster` CTAs the weight slabs -- identical for every
+// tile -- are fetched from L2 once per cluster: each CTA loads 1/cluster of a slab and multicasts
+// it into the shared memory of all CTAs of the cluster.
 template <int COUT, bool SPLIT>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ ConvParams P) {
@@ -205,33 +233,40 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 1000);
   float* s_bias = reinterpret_cast<float*>(smem + 1024);
   constexpr int kBiasBytes = ((COUT * 4 + 127) / 128) * 128;
-  const int n_a = P.n_a, n_b = P.n_b;
+  const int n_a = P.n_a, n_b = P.n_b, n_buf = P.n_buf;
   const uint32_t a_plane_bytes = (uint32_t)P.patch_rows * 16u;
   const uint32_t a_stage_bytes = a_plane_bytes * (SPLIT ? 4u : 2u);
   const uint32_t a_stage_stride = (a_stage_bytes + 127u) & ~127u;
   constexpr uint32_t kBHalf = 2u * COUT * 16u;            // one of {w_hi, w_lo}: 2 planes
-  constexpr uint32_t kBSlabGlobal = 2u * kBHalf;          // packed slab always holds hi and lo
-  constexpr uint32_t kBStage = SPLIT ? 2u * kBHalf : kBHalf;
+  constexpr uint32_t kBSlab = SPLIT ? 2u * kBHalf : kBHalf;   // bytes of one (stage, tap) slab in this mode
+  const int G = P.bgroup;                                    // slabs per B pipeline stage
+  const uint32_t b_stage_bytes = (uint32_t)G * kBSlab;
   uint8_t* a_base = smem + 1024 + kBiasBytes;
   uint8_t* b_base = a_base + (size_t)n_a * a_stage_stride;
 
-  // barrier indices
   const uint32_t bar0 = smem_u32(bars);
   auto a_full = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   auto a_empty = [&](int i) { return bar0 + 8u * (uint32_t)(n_a + i); };
   auto b_full = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + i); };
   auto b_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + n_b + i); };
-  const uint32_t acc_full = bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b);
+  auto acc_full = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + i); };
+  auto acc_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + 2 + i); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long q0 = (long long)blockIdx.x * P.S * 128;
-  const uint32_t tmem_cols = (uint32_t)(P.S * COUT) <= 32u ? 32u
-                             : (uint32_t)(P.S * COUT) <= 64u ? 64u
-                             : (uint32_t)(P.S * COUT) <= 128u ? 128u
-                             : (uint32_t)(P.S * COUT) <= 256u ? 256u : 512u;
+  const uint32_t cl = (uint32_t)P.cluster;
+  uint32_t cta_rank = 0;
+  if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+  const uint16_t cta_mask = (uint16_t)((1u << cl) - 1u);
+  const int mc = P.S * 128;
+  const uint32_t buf_cols = (uint32_t)(P.S * COUT);
+  const uint32_t want_cols = buf_cols * (uint32_t)n_buf;
+  const uint32_t tmem_cols = want_cols <= 32u ? 32u : want_cols <= 64u ? 64u : want_cols <= 128u ? 128u
+                             : want_cols <= 256u ? 256u : 512u;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 2 * n_a + 2 * n_b + 1; ++i) mbar_init(bar0 + 8u * i, 1);
+    for (int i = 0; i < n_a; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); }
+    for (int i = 0; i < n_b; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), cl); }
+    for (int i = 0; i < 2; ++i) { mbar_init(acc_full(i), 1); mbar_init(acc_empty(i), 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -246,39 +281,57 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   }
   tc_fence_before();
   __syncthreads();
+  if (cl > 1) cluster_sync_all();   // peers' barriers must be initialised before anything is multicast
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0 && lane == 0) {
     // ===== A-patch producer: one 16-channel slice (2 planes hi [+2 planes lo]) per stage =====
-    for (int i = 0; i < P.n_stages; ++i) {
-      const int slot = i % n_a;
-      const uint32_t ph = (uint32_t)(i / n_a) & 1u;
-      mbar_wait(a_empty(slot), ph ^ 1u);
-      mbar_expect_tx(a_full(slot), a_stage_bytes);
-      const FlatTensor& T = P.src[P.st_src[i]];
-      const uint8_t* g = T.base + (long long)(2 * P.st_chunk[i]) * T.plane_stride +
-                         ((long long)T.guard + q0 + P.lo_shift) * 16;
-      const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride);
-      bulk_g2s(dst, g, a_plane_bytes, a_full(slot));
-      bulk_g2s(dst + a_plane_bytes, g + T.plane_stride, a_plane_bytes, a_full(slot));
-      if (SPLIT) {
-        bulk_g2s(dst + 2 * a_plane_bytes, g + T.lo_offset, a_plane_bytes, a_full(slot));
-        bulk_g2s(dst + 3 * a_plane_bytes, g + T.lo_offset + T.plane_stride, a_plane_bytes,
-                 a_full(slot));
+    int it = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      const long long q0 = (long long)tile * mc;
+      for (int i = 0; i < P.n_stages; ++i, ++it) {
+        const int slot = it % n_a;
+        mbar_wait(a_empty(slot), ((uint32_t)(it / n_a) & 1u) ^ 1u);
+        mbar_expect_tx(a_full(slot), a_stage_bytes);
+        const FlatTensor& T = P.src[P.st_src[i]];
+        const uint8_t* g = T.base + (long long)(2 * P.st_chunk[i]) * T.plane_stride +
+                           ((long long)T.guard + q0 + P.lo_shift) * 16;
+        const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride);
+        bulk_g2s(dst, g, a_plane_bytes, a_full(slot));
+        bulk_g2s(dst + a_plane_bytes, g + T.plane_stride, a_plane_bytes, a_full(slot));
+        if (SPLIT) {
+          bulk_g2s(dst + 2 * a_plane_bytes, g + T.lo_offset, a_plane_bytes, a_full(slot));
+          bulk_g2s(dst + 3 * a_plane_bytes, g + T.lo_offset + T.plane_stride, a_plane_bytes,
+                   a_full(slot));
+        }
       }
     }
   } else if (warp == 1 && lane == 0) {
-    // ===== weight-slab producer: one (stage, tap) slab per B stage =====
-    int k = 0;
-    for (int i = 0; i < P.n_stages; ++i) {
-      for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
-        const int slot = k % n_b;
-        const uint32_t ph = (uint32_t)(k / n_b) & 1u;
-        mbar_wait(b_empty(slot), ph ^ 1u);
-        mbar_expect_tx(b_full(slot), kBStage);
-        bulk_g2s(smem_u32(b_base + (size_t)slot * kBStage), P.weights + (size_t)k * kBSlabGlobal,
-                 kBStage, b_full(slot));
+    // ===== weight-slab producer: one (stage, tap) slab per B stage, multicast over the cluster =====
+    // (up to G consecutive taps of one stage travel as one bulk copy; the packed blob of this
+    // numeric mode is contiguous in program order)
+    int kb = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      int k = 0;
+      for (int i = 0; i < P.n_stages; ++i) {
+        const int nt = P.st_ntaps[i];
+        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
+          const int n = min(G, nt - t0);
+          const int slot = kb % n_b;
+          mbar_wait(b_empty(slot), ((uint32_t)(kb / n_b) & 1u) ^ 1u);
+          const uint32_t bytes = (uint32_t)n * kBSlab;
+          mbar_expect_tx(b_full(slot), bytes);
+          const uint32_t dst = smem_u32(b_base + (size_t)slot * b_stage_bytes);
+          const uint8_t* src = P.weights + (size_t)k * kBSlab;
+          if (cl == 1) {
+            bulk_g2s(dst, src, bytes, b_full(slot));
+          } else {
+            const uint32_t part = bytes / cl;
+            bulk_g2s_multicast(dst + cta_rank * part, src + cta_rank * part, part, b_full(slot), cta_mask);
+          }
+          k += n;
+        }
       }
     }
   } else if (warp == 2) {
@@ -291,76 +344,100 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
     const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
     const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)(((COUT * 16u) >> 4) & 0x3FFF) << 16);
-    int k = 0;
-    uint32_t any = 0;
-    for (int i = 0; i < P.n_stages; ++i) {
-      const int aslot = i % n_a;
-      mbar_wait(a_full(aslot), (uint32_t)(i / n_a) & 1u);
-      const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
-      const bool skip_hilo = SPLIT && (P.st_flags[i] & 1);   // identity (residual) slabs have w_lo == 0
-      for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
-        const int bslot = k % n_b;
-        mbar_wait(b_full(bslot), (uint32_t)(k / n_b) & 1u);
-        tc_fence_after();
-        const uint32_t b_s = smem_u32(b_base + (size_t)bslot * kBStage);
-        const uint64_t b_hi = b_desc_base | (uint64_t)((b_s >> 4) & 0x3FFF);
-        const uint64_t b_lo = b_desc_base | (uint64_t)(((b_s + kBHalf) >> 4) & 0x3FFF);
-        const int shift = (int)P.tap_shift[P.st_tap0[i] + t] - P.lo_shift;
-        const uint32_t a_row0 = a_s + (uint32_t)shift * 16u;
-        if (leader) {
+    int it = 0, kb = 0, tc = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
+      const int buf = tc % n_buf;
+      mbar_wait(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // epilogue drained this buffer
+      tc_fence_after();
+      const uint32_t d_base = tmem_base + (uint32_t)buf * buf_cols;
+      uint32_t any = 0;
+      for (int i = 0; i < P.n_stages; ++i, ++it) {
+        const int aslot = it % n_a;
+        mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
+        const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
+        const bool skip_hilo = SPLIT && (P.st_flags[i] & 1);   // identity (residual) slabs have w_lo == 0
+        const int nt = P.st_ntaps[i];
+        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
+          const int n = min(G, nt - t0);
+          const int bslot = kb % n_b;
+          mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          tc_fence_after();
+          const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
+          if (leader) {
 #pragma unroll 1
-          for (int s = 0; s < P.S; ++s) {
-            const uint32_t a_row = a_row0 + (uint32_t)s * 2048u;
-            const uint64_t a_hi = a_desc_base | (uint64_t)((a_row >> 4) & 0x3FFF);
-            const uint32_t d = tmem_base + (uint32_t)(s * COUT);
-            tc_mma_bf16(d, a_hi, b_hi, idesc, any);
-            if (SPLIT) {
-              const uint64_t a_lo = a_desc_base | (uint64_t)(((a_row + 2u * a_plane_bytes) >> 4) & 0x3FFF);
-              if (!skip_hilo) tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
-              tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
+            for (int j = 0; j < n; ++j) {
+              const uint32_t b_s = b_s0 + (uint32_t)j * kBSlab;
+              const uint64_t b_hi = b_desc_base | (uint64_t)((b_s >> 4) & 0x3FFF);
+              const uint64_t b_lo = b_desc_base | (uint64_t)(((b_s + kBHalf) >> 4) & 0x3FFF);
+              const int shift = (int)P.tap_shift[P.st_tap0[i] + t0 + j] - P.lo_shift;
+              const uint32_t a_row0 = a_s + (uint32_t)shift * 16u;
+#pragma unroll 1
+              for (int s = 0; s < P.S; ++s) {
+                const uint32_t a_row = a_row0 + (uint32_t)s * 2048u;
+                const uint64_t a_hi = a_desc_base | (uint64_t)((a_row >> 4) & 0x3FFF);
+                const uint32_t d = d_base + (uint32_t)(s * COUT);
+                tc_mma_bf16(d, a_hi, b_hi, idesc, any);
+                if (SPLIT) {
+                  const uint64_t a_lo = a_desc_base | (uint64_t)(((a_row + 2u * a_plane_bytes) >> 4) & 0x3FFF);
+                  if (!skip_hilo) tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
+                  tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
+                }
+              }
+              any = 1u;
             }
+            if (cl == 1) tc_commit(b_empty(bslot));
+            else tc_commit_multicast(b_empty(bslot), cta_mask);   // frees the slot in every CTA of the cluster
           }
-          tc_commit(b_empty(bslot));
+          any = 1u;
+          __syncwarp();
         }
-        any = 1u;
+        if (leader) tc_commit(a_empty(aslot));
         __syncwarp();
       }
-      if (leader) tc_commit(a_empty(aslot));
+      if (leader) tc_commit(acc_full(buf));
       __syncwarp();
     }
-    if (leader) tc_commit(acc_full);
-    __syncwarp();
   } else if (warp >= 4) {
-    // ===== epilogue: TMEM -> registers -> bias / residual / ReLU -> split bf16 -> global =====
-    mbar_wait(acc_full, 0u);
-    tc_fence_after();
+    // ===== epilogue: TMEM -> registers -> bias / ReLU -> split bf16 -> global =====
     const int lgrp = warp & 3;  // TMEM lane group this warp may read
-    for (int s = 0; s < P.S; ++s) {
-      const long long q = q0 + s * 128 + lgrp * 32 + lane;
-      const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
-      const FlatTensor& T = P.out[o.tensor];
+    int tc = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
+      const int buf = tc % n_buf;
+      mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
+      tc_fence_after();
+      const long long q0 = (long long)tile * mc;
+      for (int s = 0; s < P.S; ++s) {
+        const long long q = q0 + s * 128 + lgrp * 32 + lane;
+        const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
+        const FlatTensor& T = P.out[o.tensor];
 #pragma unroll 1
-      for (int c0 = 0; c0 < COUT; c0 += 32) {
-        uint32_t v[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)(s * COUT + c0);
-        tc_ld16(taddr, v);
-        tc_ld16(taddr + 16, v + 16);
-        tc_ld_wait();
-        if (o.valid) {
+        for (int c0 = 0; c0 < COUT; c0 += 32) {
+          uint32_t v[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) +
+                                 (uint32_t)buf * buf_cols + (uint32_t)(s * COUT + c0);
+          tc_ld16(taddr, v);
+          tc_ld16(taddr + 16, v + 16);
+          tc_ld_wait();
+          if (o.valid) {
 #pragma unroll
-          for (int h = 0; h < 4; ++h) {
-            float f[8];
+            for (int h = 0; h < 4; ++h) {
+              float f[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e)
-              f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], 0.0f);
-            store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
+              for (int e = 0; e < 8; ++e)
+                f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], 0.0f);
+              store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
+            }
           }
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty(buf));   // 4 arrivals (one per epilogue warp) free the buffer
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (cl > 1) cluster_sync_all();   // nobody leaves while a peer may still multicast into its smem
   if (warp == 2) {
     __syncwarp();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
@@ -372,8 +449,18 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
 static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
   size_t bias = ((size_t)cout * 4 + 127) / 128 * 128;
   size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
-  size_t b = (size_t)2 * cout * 16 * (split ? 2 : 1);
+  size_t b = (size_t)2 * cout * 16 * (split ? 2 : 1) * p.bgroup;
   return 1024 + bias + a * p.n_a + b * p.n_b;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
 }
 
 template <int COUT, bool SPLIT>
@@ -381,9 +468,21 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   const size_t smem = conv_smem_bytes(p, COUT, SPLIT);
   UMT_CUDA_TRY(cudaFuncSetAttribute(conv_umma_kernel<COUT, SPLIT>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int mc = p.S * 128;
-  const int tiles = (p.n_pos + mc - 1) / mc;
-  conv_umma_kernel<COUT, SPLIT><<<tiles, kConvThreads, smem, st>>>(p);
+  int grid = std::min(p.n_tiles, sm_count() * std::max(1, p.occ));
+  grid = std::max(p.cluster, grid / p.cluster * p.cluster);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kConvThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)p.cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  UMT_CUDA_TRY(cudaLaunchKernelEx(&cfg, conv_umma_kernel<COUT, SPLIT>, p));
   return check_launch("conv_umma_kernel");
 }
 
@@ -413,7 +512,7 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int split,
   if (x >= P.W || y >= P.H) return;
   float acc = 0.f;
   int k = 0;
-  const size_t half = (size_t)2 * cout * 16, slab = 2 * half;
+  const size_t half = (size_t)2 * cout * 16, slab = split ? 2 * half : half;
   for (int i = 0; i < P.n_stages; ++i) {
     const FlatTensor& T = P.src[P.st_src[i]];
     for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
@@ -715,11 +814,25 @@ static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Fold
   if (ns > kMaxStages || nt > kMaxTaps) return fail(UMT_ERR_INVALID, "conv program too large");
   p.n_stages = ns;
   p.lo_shift = lo;
-  // tile shape: S sub-tiles so that S*Cout TMEM columns = 256 (two CTAs can share an SM)
-  int S = std::max(1, std::min(4, 256 / L.cout));
-  S = std::min(4, S * env_int("UMT_CONV_S_SCALE", 1));
-  while (S * L.cout > 512) S >>= 1;
+  // tile shape: S sub-tiles of 128 positions.  Two accumulator buffers of S*Cout TMEM columns
+  // (epilogue/MMA overlap) except for Cout = 256, where one 512-column buffer halves the weight
+  // traffic per position instead.
+  // Tuned per output width; override with UMT_CONV_CFG<cout>="S,occ,G,cluster,nbuf" (tools/sweep_conv.py)
+  // (B200 sweep, round 1: two co-resident CTAs per SM beat one larger CTA for every width; as many
+  // taps per weight stage as shared memory allows)
+  int S = (L.cout == 32) ? 4 : (L.cout == 256) ? 1 : 2, occ = 2, G = 9, clu = 2, nbuf = 2;
+  {
+    const std::string name = "UMT_CONV_CFG" + std::to_string(L.cout);
+    if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d,%d,%d,%d", &S, &occ, &G, &clu, &nbuf);
+  }
+  occ = std::max(1, std::min(2, occ));
+  while (S > 1 && S * L.cout * occ > 512) S >>= 1;
   p.S = S;
+  p.n_buf = (2 * S * L.cout * occ <= 512) ? std::max(1, std::min(2, nbuf)) : 1;
+  p.order = 0;
+  p.occ = occ;
+  p.bgroup = std::max(1, std::min(9, G));
+  p.cluster = std::max(1, std::min(2, clu));
   p.patch_rows = S * 128 + hi - lo;
   p.phase_out = L.phase_out;
   L.n_slabs = (int)(blob.size() / ((size_t)4 * L.cout * 8));
@@ -728,6 +841,15 @@ static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Fold
   UMT_CUDA_TRY(cudaMalloc(&L.d_weights, blob.size() * 2));
   m->owned.push_back(L.d_weights);
   UMT_CUDA_TRY(cudaMemcpy(L.d_weights, blob.data(), blob.size() * 2, cudaMemcpyHostToDevice));
+  {  // hi halves only, contiguous, for the single-product mode
+    const size_t half = (size_t)2 * L.cout * 8;
+    std::vector<uint16_t> hi((size_t)L.n_slabs * half);
+    for (int k = 0; k < L.n_slabs; ++k)
+      memcpy(&hi[(size_t)k * half], &blob[(size_t)k * 2 * half], half * 2);
+    UMT_CUDA_TRY(cudaMalloc(&L.d_weights_hi, hi.size() * 2));
+    m->owned.push_back(L.d_weights_hi);
+    UMT_CUDA_TRY(cudaMemcpy(L.d_weights_hi, hi.data(), hi.size() * 2, cudaMemcpyHostToDevice));
+  }
   L.d_bias = upload(m, bias);
   if (!L.d_bias) return UMT_ERR_CUDA;
   return UMT_OK;
@@ -789,7 +911,7 @@ static long long plane_rows(int H, int n_img, int* guard_out) {
   const int Wp = H + 1;
   const int guard = ((Wp + 2 + 7) / 8) * 8;
   const long long pos = (long long)n_img * Wp * Wp;
-  const long long padded = (pos + 511) / 512 * 512;
+  const long long padded = (pos + 1023) / 1024 * 1024;   // whole tiles for every cluster (512 x 2)
   *guard_out = guard;
   return guard + padded + guard + 8;
 }
@@ -854,19 +976,23 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool
   }
   if (L.res_buf >= 0) p.src[2] = m->buf[g][L.res_buf];
   p.res.base = nullptr;
-  p.weights = L.d_weights;
+  p.weights = split ? L.d_weights : L.d_weights_hi;
   p.bias = L.d_bias;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);
   // pipeline depths from the shared-memory budget
-  const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", 100) * 1024;
+  const int mc = p.S * 128;
+  p.n_tiles = ((p.n_pos + mc - 1) / mc + p.cluster - 1) / p.cluster * p.cluster;
+  const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 108 : 200) * 1024;
   const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
-  const size_t b = (size_t)2 * L.cout * 16 * (split ? 2 : 1);
   const size_t fixed = 1024 + ((size_t)L.cout * 4 + 127) / 128 * 128;
-  int n_a = 3;
+  const size_t slab = (size_t)2 * L.cout * 16 * (split ? 2 : 1);
+  while (p.bgroup > 1 && fixed + a * 2 + slab * p.bgroup * 3 > budget) --p.bgroup;   // keep >= 3 B stages
+  const size_t b = slab * p.bgroup;
+  int n_a = env_int("UMT_CONV_NA", 3);
   while (n_a > 2 && fixed + a * n_a + b * 4 > budget) --n_a;
   long long nb = ((long long)budget - (long long)fixed - (long long)(a * n_a)) / (long long)b;
   p.n_a = n_a;
-  p.n_b = (int)std::max(3LL, std::min(12LL, nb));
+  p.n_b = (int)std::max(3LL, std::min((long long)env_int("UMT_CONV_NB_MAX", 24), nb));
 }
 
 int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, float* features,

@@ -43,6 +43,12 @@ struct ConvParams {
   int lo_shift;             // most negative tap shift (rows)
   int patch_rows;           // S*128 + hi_shift - lo_shift
   int n_a, n_b;             // pipeline depths (A patches, B slabs)
+  int bgroup;               // weight slabs (taps) per B pipeline stage
+  int n_buf;                // TMEM accumulator buffers (1 or 2)
+  int cluster;              // CTAs per cluster sharing (multicasting) the weight slabs
+  int order;                // MMA issue order inside a slab: 0 sub-tile major, 1 product major
+  int occ;                  // CTAs per SM the grid is sized for
+  int n_tiles;              // tiles of S*128 positions, padded to a multiple of `cluster`
   int n_stages;
   int phase_out;            // 1: scatter the output into four (H/2, W/2) parity-phase tensors
   uint8_t st_src[kMaxStages], st_chunk[kMaxStages], st_ntaps[kMaxStages], st_tap0[kMaxStages];
@@ -58,6 +64,7 @@ struct ConvLayer {
   int phase_out = 0;
   int n_slabs = 0;
   uint8_t* d_weights = nullptr;                   // packed [slab][hi|lo][2][cout][8] bf16
+  uint8_t* d_weights_hi = nullptr;                // packed [slab][2][cout][8] bf16 (hi only)
   float* d_bias = nullptr;
   ConvParams prog{};                              // program template (tensors filled per call)
 };
