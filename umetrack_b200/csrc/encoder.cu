@@ -37,6 +37,7 @@
 #include <string>
 
 #include "model.cuh"
+#include "flat.cuh"
 
 namespace umt {
 
@@ -145,47 +146,6 @@ __device__ __forceinline__ void tc_ld_wait() {
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
   return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
          ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
-}
-
-__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
-  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&t);
-}
-__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
-
-// split 8 floats into 8 bf16 hi (+ 8 bf16 lo) and store them as 16-byte rows
-template <bool SPLIT>
-__device__ __forceinline__ void store_row8(const FlatTensor& t, int plane, long long row,
-                                           const float* v) {
-  uint8_t* p = t.base + (long long)plane * t.plane_stride + (t.guard + row) * 16;
-  uint4 h;
-  h.x = pack_bf16x2(v[0], v[1]);
-  h.y = pack_bf16x2(v[2], v[3]);
-  h.z = pack_bf16x2(v[4], v[5]);
-  h.w = pack_bf16x2(v[6], v[7]);
-  *reinterpret_cast<uint4*>(p) = h;
-  if (SPLIT) {
-    uint4 l;
-    l.x = pack_bf16x2(v[0] - bf16_lo(h.x), v[1] - bf16_hi(h.x));
-    l.y = pack_bf16x2(v[2] - bf16_lo(h.y), v[3] - bf16_hi(h.y));
-    l.z = pack_bf16x2(v[4] - bf16_lo(h.z), v[5] - bf16_hi(h.z));
-    l.w = pack_bf16x2(v[6] - bf16_lo(h.w), v[7] - bf16_hi(h.w));
-    *reinterpret_cast<uint4*>(p + t.lo_offset) = l;
-  }
-}
-
-template <bool SPLIT>
-__device__ __forceinline__ void load_row8(const FlatTensor& t, int plane, long long row, float* v) {
-  const uint8_t* p = t.base + (long long)plane * t.plane_stride + (t.guard + row) * 16;
-  uint4 h = *reinterpret_cast<const uint4*>(p);
-  v[0] = bf16_lo(h.x); v[1] = bf16_hi(h.x); v[2] = bf16_lo(h.y); v[3] = bf16_hi(h.y);
-  v[4] = bf16_lo(h.z); v[5] = bf16_hi(h.z); v[6] = bf16_lo(h.w); v[7] = bf16_hi(h.w);
-  if (SPLIT) {
-    uint4 l = *reinterpret_cast<const uint4*>(p + t.lo_offset);
-    v[0] += bf16_lo(l.x); v[1] += bf16_hi(l.x); v[2] += bf16_lo(l.y); v[3] += bf16_hi(l.y);
-    v[4] += bf16_lo(l.z); v[5] += bf16_hi(l.z); v[6] += bf16_lo(l.w); v[7] += bf16_hi(l.w);
-  }
 }
 
 // position -> (valid, destination tensor index, destination row)
@@ -410,21 +370,23 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
         const long long q = q0 + s * 128 + lgrp * 32 + lane;
         const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
         const FlatTensor& T = P.out[o.tensor];
+        constexpr int kStep = (COUT % 32 == 0) ? 32 : 16;   // columns per TMEM round trip
+        const float lo_clamp = P.relu ? 0.0f : -INFINITY;
 #pragma unroll 1
-        for (int c0 = 0; c0 < COUT; c0 += 32) {
-          uint32_t v[32];
+        for (int c0 = 0; c0 < COUT; c0 += kStep) {
+          uint32_t v[kStep];
           const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) +
                                  (uint32_t)buf * buf_cols + (uint32_t)(s * COUT + c0);
           tc_ld16(taddr, v);
-          tc_ld16(taddr + 16, v + 16);
+          if (kStep == 32) tc_ld16(taddr + 16, v + 16);
           tc_ld_wait();
           if (o.valid) {
 #pragma unroll
-            for (int h = 0; h < 4; ++h) {
+            for (int h = 0; h < kStep / 8; ++h) {
               float f[8];
 #pragma unroll
               for (int e = 0; e < 8; ++e)
-                f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], 0.0f);
+                f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
               store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
             }
           }
@@ -486,14 +448,18 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   return check_launch("conv_umma_kernel");
 }
 
-static int launch_conv(const ConvParams& p, int cout, bool split, cudaStream_t st) {
+int launch_conv(const ConvParams& p, int cout, bool split, cudaStream_t st) {
   switch (cout) {
     case 32: return split ? launch_conv_t<32, true>(p, st) : launch_conv_t<32, false>(p, st);
     case 64: return split ? launch_conv_t<64, true>(p, st) : launch_conv_t<64, false>(p, st);
     case 128: return split ? launch_conv_t<128, true>(p, st) : launch_conv_t<128, false>(p, st);
     case 256: return split ? launch_conv_t<256, true>(p, st) : launch_conv_t<256, false>(p, st);
+    // widths of the fusion / temporal / regressor layers (always fp32-equivalent)
+    case 80: if (split) return launch_conv_t<80, true>(p, st); break;
+    case 96: if (split) return launch_conv_t<96, true>(p, st); break;
+    case 112: if (split) return launch_conv_t<112, true>(p, st); break;
   }
-  return fail(UMT_ERR_UNSUPPORTED, "conv: unsupported Cout %d", cout);
+  return fail(UMT_ERR_UNSUPPORTED, "conv: unsupported Cout %d (split=%d)", cout, (int)split);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -668,10 +634,6 @@ static inline float bf2f(uint16_t h) {
   return f;
 }
 
-struct Folded {           // conv weight with BatchNorm folded in: w'[co][ci][k], b'[co]
-  std::vector<float> w, b;
-  int cout, cin, ks;
-};
 
 static Folded fold_conv_bn(const float* w, const float* conv_bias, const float* gamma,
                            const float* beta, const float* mean, const float* var, int cout,
@@ -741,11 +703,12 @@ static void pack_identity_slab(std::vector<uint16_t>& blob, int cout, int chunk)
 }
 
 // Build program + packed weights of one backbone convolution.
-static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds) {
+int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds) {
   ConvParams& p = L.prog;
   memset(&p, 0, sizeof(p));
   const int H = kStageHW[L.geom], W = H, Wp = W + 1;
   p.H = H; p.W = W;
+  p.relu = L.relu;
   std::vector<uint16_t> blob;
   int ns = 0, nt = 0, lo = 0, hi = 0;
   auto add_tap = [&](int shift) {
@@ -753,7 +716,14 @@ static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Fold
     lo = std::min(lo, shift);
     hi = std::max(hi, shift);
   };
-  if (L.stride == 1) {
+  if (main.ks == 1) {   // pointwise convolution: one tap, no halo
+    add_tap(0);
+    for (int c = 0; c < main.cin / 16; ++c) {
+      p.st_src[ns] = 0; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = 1; p.st_tap0[ns] = 0;
+      ++ns;
+      pack_slab(blob, main, c, 0, 0);
+    }
+  } else if (L.stride == 1) {
     for (int ky = 0; ky < 3; ++ky)
       for (int kx = 0; kx < 3; ++kx) add_tap((ky - 1) * Wp + (kx - 1));
     for (int c = 0; c < main.cin / 16; ++c) {
@@ -820,7 +790,7 @@ static int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Fold
   // Tuned per output width; override with UMT_CONV_CFG<cout>="S,occ,G,cluster,nbuf" (tools/sweep_conv.py)
   // (B200 sweep, round 1: two co-resident CTAs per SM beat one larger CTA for every width; as many
   // taps per weight stage as shared memory allows)
-  int S = (L.cout == 32) ? 4 : (L.cout == 256) ? 1 : 2, occ = 2, G = 9, clu = 2, nbuf = 2;
+  int S = (L.cout == 32) ? 4 : (L.cout == 256 || L.cout % 32 != 0 || L.cout == 96) ? 1 : 2, occ = 2, G = 9, clu = 2, nbuf = 2;
   {
     const std::string name = "UMT_CONV_CFG" + std::to_string(L.cout);
     if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d,%d,%d,%d", &S, &occ, &G, &clu, &nbuf);
@@ -916,9 +886,27 @@ static long long plane_rows(int H, int n_img, int* guard_out) {
   return guard + padded + guard + 8;
 }
 
+size_t flat_tensor_bytes(int H, int C, int n_img) {
+  int g;
+  return (size_t)plane_rows(H, n_img, &g) * 16 * (C / 8) * 2;
+}
+FlatTensor make_flat_tensor(uint8_t* base, int H, int C, int n_img);
+
 static size_t flat_bytes(int H, int C, int n_img) {
   int g;
   return (size_t)plane_rows(H, n_img, &g) * 16 * (C / 8) * 2;
+}
+
+FlatTensor make_flat_tensor(uint8_t* base, int H, int C, int n_img) {
+  FlatTensor t;
+  int g;
+  const long long rows = plane_rows(H, n_img, &g);
+  t.base = base;
+  t.plane_stride = rows * 16;
+  t.lo_offset = t.plane_stride * (C / 8);
+  t.guard = g;
+  t.pad_ = 0;
+  return t;
 }
 
 static FlatTensor make_flat(uint8_t* base, int H, int C, int n_img) {
@@ -959,6 +947,9 @@ void encoder_bind(umt_model* m, uint8_t* base) {
   }
 }
 
+// pipeline depths etc. once tensors, weights and n_pos are known
+void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split);
+
 static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool split,
                          ConvParams& p) {
   p = L.prog;
@@ -979,6 +970,10 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool
   p.weights = split ? L.d_weights : L.d_weights_hi;
   p.bias = L.d_bias;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);
+  finalize_conv_params(p, L, split);
+}
+
+void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split) {
   // pipeline depths from the shared-memory budget
   const int mc = p.S * 128;
   p.n_tiles = ((p.n_pos + mc - 1) / mc + p.cluster - 1) / p.cluster * p.cluster;

@@ -1,0 +1,52 @@
+// Device helpers for the planar flat activation layout (see model.cuh): 16-byte rows of 8 bf16
+// channels, values kept as hi (+ lo) bf16 pairs.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "model.cuh"
+
+namespace umt {
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
+
+// split 8 floats into 8 bf16 hi (+ 8 bf16 lo) and store them as 16-byte rows
+template <bool SPLIT>
+__device__ __forceinline__ void store_row8(const FlatTensor& t, int plane, long long row,
+                                           const float* v) {
+  uint8_t* p = t.base + (long long)plane * t.plane_stride + (t.guard + row) * 16;
+  uint4 h;
+  h.x = pack_bf16x2(v[0], v[1]);
+  h.y = pack_bf16x2(v[2], v[3]);
+  h.z = pack_bf16x2(v[4], v[5]);
+  h.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(p) = h;
+  if (SPLIT) {
+    uint4 l;
+    l.x = pack_bf16x2(v[0] - bf16_lo(h.x), v[1] - bf16_hi(h.x));
+    l.y = pack_bf16x2(v[2] - bf16_lo(h.y), v[3] - bf16_hi(h.y));
+    l.z = pack_bf16x2(v[4] - bf16_lo(h.z), v[5] - bf16_hi(h.z));
+    l.w = pack_bf16x2(v[6] - bf16_lo(h.w), v[7] - bf16_hi(h.w));
+    *reinterpret_cast<uint4*>(p + t.lo_offset) = l;
+  }
+}
+
+template <bool SPLIT>
+__device__ __forceinline__ void load_row8(const FlatTensor& t, int plane, long long row, float* v) {
+  const uint8_t* p = t.base + (long long)plane * t.plane_stride + (t.guard + row) * 16;
+  uint4 h = *reinterpret_cast<const uint4*>(p);
+  v[0] = bf16_lo(h.x); v[1] = bf16_hi(h.x); v[2] = bf16_lo(h.y); v[3] = bf16_hi(h.y);
+  v[4] = bf16_lo(h.z); v[5] = bf16_hi(h.z); v[6] = bf16_lo(h.w); v[7] = bf16_hi(h.w);
+  if (SPLIT) {
+    uint4 l = *reinterpret_cast<const uint4*>(p + t.lo_offset);
+    v[0] += bf16_lo(l.x); v[1] += bf16_hi(l.x); v[2] += bf16_lo(l.y); v[3] += bf16_hi(l.y);
+    v[4] += bf16_lo(l.z); v[5] += bf16_hi(l.z); v[6] += bf16_lo(l.w); v[7] += bf16_hi(l.w);
+  }
+}
+
+
+}  // namespace umt

@@ -155,13 +155,15 @@ extern "C" void umt_model_destroy(umt_model* m) {
   delete m;
 }
 
+// tail scratch: dense features, three 6x6 planar flat tensors of 144 channels, skeleton maps
 static size_t tail_bytes(int max_images, int max_samples, size_t* feats_off, size_t* a_off,
                          size_t* b_off, size_t* c_off, size_t* s_off) {
   size_t o = 0;
+  const size_t flat = align256(flat_tensor_bytes(6, 144, max_samples));
   *feats_off = o; o += align256((size_t)max_images * 72 * 36 * 4);
-  *a_off = o; o += align256((size_t)max_samples * 144 * 36 * 4);
-  *b_off = o; o += align256((size_t)max_samples * 144 * 36 * 4);
-  *c_off = o; o += align256((size_t)max_samples * 144 * 36 * 4);
+  *a_off = o; o += flat;
+  *b_off = o; o += flat;
+  *c_off = o; o += flat;
   *s_off = o; o += align256((size_t)max_samples * 4 * 36 * 4);
   return o;
 }
@@ -196,9 +198,9 @@ extern "C" int umt_model_bind_workspace(umt_model* m, void* workspace, size_t by
   tail_bytes(max_images, max_samples, &f, &a, &b, &c, &s);
   uint8_t* t = m->ws + encoder_workspace_bytes(chunk_images);
   m->feats = (float*)(t + f);
-  m->tail_a = (float*)(t + a);
-  m->tail_b = (float*)(t + b);
-  m->tail_c = (float*)(t + c);
+  m->tail_flat[0] = make_flat_tensor(t + a, 6, 144, max_samples);
+  m->tail_flat[1] = make_flat_tensor(t + b, 6, 144, max_samples);
+  m->tail_flat[2] = make_flat_tensor(t + c, 6, 144, max_samples);
   m->tail_skel = (float*)(t + s);
   return UMT_OK;
 }

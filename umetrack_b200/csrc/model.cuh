@@ -51,6 +51,7 @@ struct ConvParams {
   int n_tiles;              // tiles of S*128 positions, padded to a multiple of `cluster`
   int n_stages;
   int phase_out;            // 1: scatter the output into four (H/2, W/2) parity-phase tensors
+  int relu;                 // 1: ReLU in the epilogue
   uint8_t st_src[kMaxStages], st_chunk[kMaxStages], st_ntaps[kMaxStages], st_tap0[kMaxStages];
   uint8_t st_flags[kMaxStages];   // bit 0: weight slab has no lo part (identity slab of a residual)
   short tap_shift[kMaxTaps];
@@ -62,11 +63,17 @@ struct ConvLayer {
   int src_kind = 0;                               // 0: flat buffer, 1: phase tensors
   int src_buf = 0, out_buf = 0, res_buf = -1;     // buffer ids within the geometry
   int phase_out = 0;
+  int relu = 1;
   int n_slabs = 0;
   uint8_t* d_weights = nullptr;                   // packed [slab][hi|lo][2][cout][8] bf16
   uint8_t* d_weights_hi = nullptr;                // packed [slab][2][cout][8] bf16 (hi only)
   float* d_bias = nullptr;
   ConvParams prog{};                              // program template (tensors filled per call)
+};
+
+struct Folded {           // conv weight with BatchNorm folded in: w[co][ci][ks*ks], b[co]
+  std::vector<float> w, b;
+  int cout, cin, ks;
 };
 
 struct TailWeights {
@@ -101,10 +108,9 @@ struct umt_model {
   umt::FlatTensor buf[4][3]{};            // per geometry: ping, pong, mid
   umt::FlatTensor phase[4][4]{};          // phase[g]: input of geometry g (g=1..3), 4 parities
   float* feats = nullptr;                 // [max_images,72,36]
-  float* tail_a = nullptr;                // [max_samples,144,36]
-  float* tail_b = nullptr;                // [max_samples,144,36]
-  float* tail_c = nullptr;                // [max_samples,144,36]
   float* tail_skel = nullptr;             // [max_samples,4,36]
+  std::vector<umt::ConvLayer> tail_convs; // fusion(3), temporal(3), regressor_k(4), regressor_u(4)
+  umt::FlatTensor tail_flat[3]{};         // 6x6 planar flat scratch, 144 channels capacity
   int launches = 0;
 };
 
@@ -117,6 +123,11 @@ int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, 
                         float* out_simt, float* out_umma, int* shape, cudaStream_t st);
 size_t encoder_workspace_bytes(int chunk_images);
 void encoder_bind(umt_model* m, uint8_t* base);
+int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds);
+int launch_conv(const ConvParams& p, int cout, bool split, cudaStream_t st);
+void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split);
+size_t flat_tensor_bytes(int H, int C, int n_img);
+FlatTensor make_flat_tensor(uint8_t* base, int H, int C, int n_img);
 // tail.cu
 int tail_build(umt_model* m, const float* const* t);
 int tail_forward(umt_model* m, int head, const float* feats, const float* intrinsics,

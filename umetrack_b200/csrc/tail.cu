@@ -1,5 +1,9 @@
-// Stage (b), part 2: everything after the per-view encoder, in float32 on CUDA cores (1 % of the
-// FLOPs, and the part whose values must stay float32: FTL transforms, memory bank, Procrustes).
+// Stage (b), part 2: everything after the per-view encoder (1 % of the FLOPs).  The ten
+// convolutions (fusion 1x1 x3, temporal 1x1 x3, regressor 3x3 x4) run through the same tensor-core
+// kernel as the backbone, always in the fp32-equivalent split-bf16 mode, on 6x6 planar flat
+// tensors whose channel counts are padded to multiples of 16 with zero weights; the glue between
+// them (FTL transforms, memory bank, skeleton encoder, decoders, Procrustes) is float32/float64
+// CUDA-core code.
 //   feature-transform layer + two-view fusion   lib/models/feature_extractor.py:61-141,
 //                                                lib/models/model_utils.py:57-104,141-192
 //   temporal memory (SimpleConvRNN)              lib/models/temporal.py:51-139
@@ -7,21 +11,19 @@
 //   pose regressor + decoders + Procrustes       lib/models/regressor.py:76-186,
 //                                                lib/models/model_utils.py:17-54
 //   world-space recovery / right-hand un-mirror  lib/models/umetrack_model.py:77-97
-// All feature maps are dense float32 [batch, C, 36] (NCHW with 6x6 flattened), which is the
-// layout the reference's FTL reshape (C channels -> 3 x C/3*36 points) is defined on.
-//
-// The convolutions use one thread per (sample, output channel) holding all 36 output pixels in
-// registers: per input channel a thread reads its weights once and the input map with 16-byte
-// shared-memory broadcasts, so the inner loop is FMA bound.
+// The glue kernels work on one sample per CTA with the sample's [C][36] tile in shared memory
+// (channel-major, the layout the reference's FTL reshape "C channels -> 3 x C/3*36 points" is
+// defined on) and convert from/to the planar flat layout with 16-byte rows.
 #include <cmath>
 #include <string>
 
 #include "model.cuh"
+#include "flat.cuh"
 
 namespace umt {
 
 constexpr int kPix = 36;
-constexpr int kSamplesPerBlock = 4;
+constexpr int kPos = 49;   // positions per sample in the 6x6 planar flat raster (7 x 7)
 
 // ------------------------------------------------------------------------------------------
 // small matrix helpers (double precision, per thread)
@@ -86,19 +88,47 @@ __device__ __forceinline__ void ftl_point(const float* xf, float x, float y, flo
 }
 
 // ------------------------------------------------------------------------------------------
+// sample tile <-> planar flat (6x6 geometry, split bf16)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ long long flat_row6(int b, int p) { return (long long)b * kPos + (p / 6) * 7 + (p % 6); }
+
+// tile[(plane*8+e)*36 + p] <- tensor
+__device__ void load_sample_tile(const FlatTensor& T, int b, int nplanes, float* tile) {
+  for (int i = threadIdx.x; i < nplanes * kPix; i += blockDim.x) {
+    const int pl = i / kPix, p = i % kPix;
+    float v[8];
+    load_row8<true>(T, pl, flat_row6(b, p), v);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) tile[(pl * 8 + e) * kPix + p] = v[e];
+  }
+}
+
+__device__ void store_sample_tile(const FlatTensor& T, int b, int nplanes, const float* tile) {
+  for (int i = threadIdx.x; i < nplanes * kPix; i += blockDim.x) {
+    const int pl = i / kPix, p = i % kPix;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = tile[(pl * 8 + e) * kPix + p];
+    store_row8<true>(T, pl, flat_row6(b, p), v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // 1. views -> canonical space, channel-concatenated for the fusion convs
-//    (feature_extractor.py:61-87,121-133).  One CTA per sample.
+//    (feature_extractor.py:61-87,121-133).  One CTA per sample; output 144 channels.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 fuse_prepare_kernel(const float* __restrict__ feats, const float* __restrict__ intrinsics,
                     const float* __restrict__ extrinsics, const int64_t* __restrict__ sample_range,
-                    float* __restrict__ canon /* [B,144,36] */) {
+                    FlatTensor canon) {
   __shared__ float sxf[2][12];
+  __shared__ float tile[144 * kPix];
   const int b = blockIdx.x;
   const int r0 = (int)sample_range[2 * b], r1 = (int)sample_range[2 * b + 1];
-  float* dst = canon + (size_t)b * 144 * kPix;
   if (r1 - r0 != 2) {  // single-view samples skip the fusion convs (feature_extractor.py:89-94)
-    for (int i = threadIdx.x; i < 144 * kPix; i += blockDim.x) dst[i] = 0.f;
+    for (int i = threadIdx.x; i < 144 * kPix; i += blockDim.x) tile[i] = 0.f;
+    __syncthreads();
+    store_sample_tile(canon, b, 18, tile);
     return;
   }
   if (threadIdx.x < 2) {
@@ -122,134 +152,40 @@ fuse_prepare_kernel(const float* __restrict__ feats, const float* __restrict__ i
     const float* src = feats + (size_t)(r0 + v) * 72 * kPix;
     float ox, oy, oz;
     ftl_point(sxf[v], src[j], src[864 + j], src[1728 + j], ox, oy, oz);
-    float* d = dst + (size_t)v * 72 * kPix;
+    float* d = tile + v * 72 * kPix;
     d[j] = ox;
     d[864 + j] = oy;
     d[1728 + j] = oz;
   }
-}
-
-// ------------------------------------------------------------------------------------------
-// 2. convolutions on 6x6 maps.  Thread = (sample, output channel), 36 accumulators.
-// ------------------------------------------------------------------------------------------
-template <int KS>
-__global__ void __launch_bounds__(kSamplesPerBlock * 112)
-conv6_kernel(const float* __restrict__ in, int in_stride /* floats per sample */, int cin,
-             const float* __restrict__ w /* [cout][cin][KS*KS] */, const float* __restrict__ bias,
-             const float* __restrict__ res, int res_stride, float* __restrict__ out, int out_stride,
-             int cout, int relu, int n_samples) {
-  // KS==1: sIn[sample][ci][36]; KS==3: sIn[sample][ci][64] zero-padded 8x8 tiles
-  extern __shared__ __align__(16) float sIn[];
-  constexpr int kTile = (KS == 1) ? 36 : 64;
-  const int s0 = blockIdx.x * kSamplesPerBlock;
-  const int ns = min(kSamplesPerBlock, n_samples - s0);
-  const int per = cin * kTile;
-  for (int i = threadIdx.x; i < kSamplesPerBlock * per; i += blockDim.x) {
-    const int s = i / per, r = i % per, ci = r / kTile, p = r % kTile;
-    float v = 0.f;
-    if (s < ns) {
-      if (KS == 1) {
-        v = in[(size_t)(s0 + s) * in_stride + ci * kPix + p];
-      } else {
-        const int y = (p >> 3) - 1, x = (p & 7) - 1;
-        if (y >= 0 && y < 6 && x >= 0 && x < 6) v = in[(size_t)(s0 + s) * in_stride + ci * kPix + y * 6 + x];
-      }
-    }
-    sIn[i] = v;
-  }
   __syncthreads();
-  const int s = threadIdx.x / 112, co = threadIdx.x % 112;
-  if (s >= ns || co >= cout) return;
-  float acc[36];
-  const float b0 = bias ? bias[co] : 0.f;
-#pragma unroll
-  for (int p = 0; p < 36; ++p) acc[p] = b0;
-  const float* xs = sIn + (size_t)s * per;
-  const float* wr = w + (size_t)co * cin * KS * KS;
-  for (int ci = 0; ci < cin; ++ci) {
-    if (KS == 1) {
-      const float ww = __ldg(wr + ci);
-      const float4* x4 = reinterpret_cast<const float4*>(xs + ci * 36);
-#pragma unroll
-      for (int q = 0; q < 9; ++q) {
-        const float4 x = x4[q];
-        acc[4 * q + 0] = fmaf(x.x, ww, acc[4 * q + 0]);
-        acc[4 * q + 1] = fmaf(x.y, ww, acc[4 * q + 1]);
-        acc[4 * q + 2] = fmaf(x.z, ww, acc[4 * q + 2]);
-        acc[4 * q + 3] = fmaf(x.w, ww, acc[4 * q + 3]);
-      }
-    } else {
-      float wk[9];
-#pragma unroll
-      for (int k = 0; k < 9; ++k) wk[k] = __ldg(wr + ci * 9 + k);
-      float t[64];
-      const float4* x4 = reinterpret_cast<const float4*>(xs + ci * 64);
-#pragma unroll
-      for (int q = 0; q < 16; ++q) {
-        const float4 x = x4[q];
-        t[4 * q] = x.x; t[4 * q + 1] = x.y; t[4 * q + 2] = x.z; t[4 * q + 3] = x.w;
-      }
-#pragma unroll
-      for (int y = 0; y < 6; ++y)
-#pragma unroll
-        for (int x = 0; x < 6; ++x) {
-          float a = acc[y * 6 + x];
-#pragma unroll
-          for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 3; ++kx) a = fmaf(t[(y + ky) * 8 + x + kx], wk[ky * 3 + kx], a);
-          acc[y * 6 + x] = a;
-        }
-    }
-  }
-  float* o = out + (size_t)(s0 + s) * out_stride + (size_t)co * kPix;
-  const float* r = res ? res + (size_t)(s0 + s) * res_stride + (size_t)co * kPix : nullptr;
-#pragma unroll
-  for (int p = 0; p < 36; ++p) {
-    float v = acc[p];
-    if (r) v += r[p];
-    if (relu) v = fmaxf(v, 0.f);
-    o[p] = v;
-  }
-}
-
-template <int KS>
-static int launch_conv6(const float* in, int in_stride, int cin, const float* w, const float* b,
-                        const float* res, int res_stride, float* out, int out_stride, int cout,
-                        int relu, int n, cudaStream_t st) {
-  if (cout > 112) return fail(UMT_ERR_UNSUPPORTED, "conv6: cout %d > 112", cout);
-  const size_t smem = (size_t)kSamplesPerBlock * cin * ((KS == 1) ? 36 : 64) * sizeof(float);
-  UMT_CUDA_TRY(cudaFuncSetAttribute(conv6_kernel<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int blocks = (n + kSamplesPerBlock - 1) / kSamplesPerBlock;
-  conv6_kernel<KS><<<blocks, kSamplesPerBlock * 112, smem, st>>>(in, in_stride, cin, w, b, res, res_stride,
-                                                                 out, out_stride, cout, relu, n);
-  return check_launch("conv6_kernel");
+  store_sample_tile(canon, b, 18, tile);
 }
 
 // ------------------------------------------------------------------------------------------
-// 3. canonical -> cam0 (feature_extractor.py:135-139) or single-view FTL (:89-94), memory warp
+// 2. canonical -> cam0 (feature_extractor.py:135-139) or single-view FTL (:89-94), memory warp
 //    and bookkeeping of SimpleConvRNN.transform_memory_features (temporal.py:51-78), and the
-//    channel concat [memory(18) | image features(72)] (temporal.py:83-85).  One CTA per sample.
+//    channel concat [memory(18) | image features(72) | 6 zero channels] (temporal.py:83-85).
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-temporal_prepare_kernel(const float* __restrict__ fused_raw /* [B,72,36] stride 144*36 */,
-                        const float* __restrict__ feats, const float* __restrict__ intrinsics,
-                        const float* __restrict__ extrinsics, const int64_t* __restrict__ sample_range,
-                        const int64_t* __restrict__ memory_idx, const uint8_t* __restrict__ use_memory,
-                        float* __restrict__ mem_state, float* __restrict__ prev_extr, int n_slots,
-                        float* __restrict__ tin /* [B,90,36] stride 144*36 */) {
+temporal_prepare_kernel(FlatTensor fused_raw /* 80 ch, 72 valid */, const float* __restrict__ feats,
+                        const float* __restrict__ intrinsics, const float* __restrict__ extrinsics,
+                        const int64_t* __restrict__ sample_range, const int64_t* __restrict__ memory_idx,
+                        const uint8_t* __restrict__ use_memory, float* __restrict__ mem_state,
+                        float* __restrict__ prev_extr, int n_slots, FlatTensor tin /* 96 ch */) {
   __shared__ float sS[12];
   __shared__ float sM[12];
   __shared__ int sUse;
+  __shared__ float sin_[72 * kPix];
+  __shared__ float sout[96 * kPix];
   const int b = blockIdx.x;
   const int r0 = (int)sample_range[2 * b], r1 = (int)sample_range[2 * b + 1];
   const int slot = (int)memory_idx[b];
-  if (slot < 0 || slot >= n_slots) return;
+  const bool slot_ok = slot >= 0 && slot < n_slots;
   if (threadIdx.x == 0) {
     for (int i = 0; i < 12; ++i) sS[i] = 0.f;
     sS[0] = sS[5] = 1.f;
     sS[10] = intrinsics[(size_t)r0 * 9] / 200.0f;
-    int use = use_memory[b] ? 1 : 0;
+    int use = (slot_ok && use_memory[b]) ? 1 : 0;
     if (use) {
       double P[16], Pinv[16], C[16], X[16];
       load_mat4(prev_extr + (size_t)slot * 16, P);
@@ -263,34 +199,40 @@ temporal_prepare_kernel(const float* __restrict__ fused_raw /* [B,72,36] stride 
     }
     sUse = use;
   }
+  const bool multi = (r1 - r0) == 2;
+  if (multi) {
+    load_sample_tile(fused_raw, b, 9, sin_);
+  } else {
+    const float* src = feats + (size_t)r0 * 72 * kPix;
+    for (int i = threadIdx.x; i < 72 * kPix; i += blockDim.x) sin_[i] = src[i];
+  }
   __syncthreads();
-  float* out = tin + (size_t)b * 144 * kPix;
-  float* mem = mem_state + (size_t)slot * 18 * kPix;
-  // memory part: 18 channels = 216 points
-  for (int j = threadIdx.x; j < 216; j += blockDim.x) {
+  const float* mem = slot_ok ? mem_state + (size_t)slot * 18 * kPix : nullptr;
+  for (int j = threadIdx.x; j < 216; j += blockDim.x) {   // memory: 18 channels = 216 points
     float ox = 0.f, oy = 0.f, oz = 0.f;
     if (sUse) ftl_point(sM, mem[j], mem[216 + j], mem[432 + j], ox, oy, oz);
-    out[j] = ox;
-    out[216 + j] = oy;
-    out[432 + j] = oz;
+    sout[j] = ox;
+    sout[216 + j] = oy;
+    sout[432 + j] = oz;
   }
-  // image-feature part: 72 channels = 864 points, transformed by S of view 0
-  const bool multi = (r1 - r0) == 2;
-  const float* src = multi ? fused_raw + (size_t)b * 144 * kPix : feats + (size_t)r0 * 72 * kPix;
-  float* o2 = out + 18 * kPix;
-  for (int j = threadIdx.x; j < 864; j += blockDim.x) {
+  float* o2 = sout + 18 * kPix;
+  for (int j = threadIdx.x; j < 864; j += blockDim.x) {   // image features: 72 channels = 864 points
     float ox, oy, oz;
-    ftl_point(sS, src[j], src[864 + j], src[1728 + j], ox, oy, oz);
+    ftl_point(sS, sin_[j], sin_[864 + j], sin_[1728 + j], ox, oy, oz);
     o2[j] = ox;
     o2[864 + j] = oy;
     o2[1728 + j] = oz;
   }
+  for (int j = threadIdx.x; j < 6 * kPix; j += blockDim.x) sout[90 * kPix + j] = 0.f;
   // prev_extrinsics[memory_idx] = cur_extrinsics (temporal.py:77)
-  if (threadIdx.x < 16) prev_extr[(size_t)slot * 16 + threadIdx.x] = extrinsics[(size_t)r0 * 16 + threadIdx.x];
+  if (slot_ok && threadIdx.x < 16)
+    prev_extr[(size_t)slot * 16 + threadIdx.x] = extrinsics[(size_t)r0 * 16 + threadIdx.x];
+  __syncthreads();
+  store_sample_tile(tin, b, 12, sout);
 }
 
 // ------------------------------------------------------------------------------------------
-// 4. skeleton encoder: Linear(132->144) -> view(4,6,6) -> BN(4) -> ReLU, BN folded on the host.
+// 3. skeleton encoder: Linear(132->144) -> view(4,6,6) -> BN(4) -> ReLU, BN folded on the host.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(144)
 skeleton_kernel(const float* __restrict__ axes, const float* __restrict__ rest,
@@ -310,31 +252,32 @@ skeleton_kernel(const float* __restrict__ axes, const float* __restrict__ rest,
 }
 
 // ------------------------------------------------------------------------------------------
-// 5. write back the memory channels and assemble the regressor input
-//    (temporal.py:87-91,134; umetrack_model.py:202-210)
+// 4. write back the memory channels and assemble the regressor input
+//    (temporal.py:87-91,134; umetrack_model.py:202-210): [72 features | 4 skeleton | zeros] = 80 ch
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-temporal_finish_kernel(const float* __restrict__ tout /* [B,90,36] stride 144*36 */,
-                       const int64_t* __restrict__ memory_idx, float* __restrict__ mem_state,
-                       int n_slots, const float* __restrict__ skel, int n_skel,
-                       float* __restrict__ rin /* [B,76|72,36] stride 144*36 */) {
+temporal_finish_kernel(FlatTensor tout /* 96 ch */, const int64_t* __restrict__ memory_idx,
+                       float* __restrict__ mem_state, int n_slots, const float* __restrict__ skel,
+                       int n_skel, FlatTensor rin /* 80 ch */) {
+  __shared__ float t[96 * kPix];
+  __shared__ float r[80 * kPix];
   const int b = blockIdx.x;
   const int slot = (int)memory_idx[b];
-  const float* t = tout + (size_t)b * 144 * kPix;
+  load_sample_tile(tout, b, 12, t);
+  __syncthreads();
   if (slot >= 0 && slot < n_slots) {
     float* mem = mem_state + (size_t)slot * 18 * kPix;
     for (int i = threadIdx.x; i < 18 * kPix; i += blockDim.x) mem[i] = t[i];
   }
-  float* r = rin + (size_t)b * 144 * kPix;
   for (int i = threadIdx.x; i < 72 * kPix; i += blockDim.x) r[i] = t[18 * kPix + i];
-  if (skel) {
-    const float* sk = skel + (size_t)(n_skel == 1 ? 0 : b) * 4 * kPix;
-    for (int i = threadIdx.x; i < 4 * kPix; i += blockDim.x) r[72 * kPix + i] = sk[i];
-  }
+  const float* sk = skel ? skel + (size_t)(n_skel == 1 ? 0 : b) * 4 * kPix : nullptr;
+  for (int i = threadIdx.x; i < 8 * kPix; i += blockDim.x) r[72 * kPix + i] = (sk && i < 4 * kPix) ? sk[i] : 0.f;
+  __syncthreads();
+  store_sample_tile(rin, b, 10, r);
 }
 
 // ------------------------------------------------------------------------------------------
-// 6. head: conv1x1(C -> n_out) + global average pool, decoders, Procrustes, world recovery
+// 5. head: conv1x1(C -> n_out) + global average pool, decoders, Procrustes, world recovery
 // ------------------------------------------------------------------------------------------
 __device__ void jacobi_svd3(const double* A, double* U, double* S, double* V) {
   // one-sided Jacobi: rotate columns of W = A*V until orthogonal; then W = U*diag(S)
@@ -411,20 +354,25 @@ __device__ double det3(const double* m) {
 }
 
 __global__ void __launch_bounds__(128)
-head_kernel(const float* __restrict__ x /* [B,C,36] stride 144*36 */, int C,
-            const float* __restrict__ w /* [n_out][C] */, const float* __restrict__ bias, int n_out,
-            int with_scale, const float* __restrict__ extrinsics,
-            const int64_t* __restrict__ sample_range, const int64_t* __restrict__ hand_idx,
-            float* __restrict__ out_angles, float* __restrict__ out_wrist,
-            float* __restrict__ out_scale, float* __restrict__ out_sigma) {
+head_kernel(FlatTensor x /* 80 ch */, int C, const float* __restrict__ w /* [n_out][C] */,
+            const float* __restrict__ bias, int n_out, int with_scale,
+            const float* __restrict__ extrinsics, const int64_t* __restrict__ sample_range,
+            const int64_t* __restrict__ hand_idx, float* __restrict__ out_angles,
+            float* __restrict__ out_wrist, float* __restrict__ out_scale,
+            float* __restrict__ out_sigma) {
   __shared__ float sMean[128];
   __shared__ float sRaw[64];
   const int b = blockIdx.x;
-  const float* xb = x + (size_t)b * 144 * kPix;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  // channel means over the 36 pixels: thread = (plane, e) reads its 16-byte rows
+  if (threadIdx.x < 80) {
+    const int pl = threadIdx.x >> 3, e = threadIdx.x & 7;
     float s = 0.f;
-    for (int p = 0; p < kPix; ++p) s += xb[c * kPix + p];
-    sMean[c] = s * (1.0f / 36.0f);
+    for (int p = 0; p < kPix; ++p) {
+      float v[8];
+      load_row8<true>(x, pl, flat_row6(b, p), v);
+      s += v[e];
+    }
+    sMean[threadIdx.x] = s * (1.0f / 36.0f);
   }
   __syncthreads();
   // conv1x1 and the average pool commute (both linear); pooling first saves 36x the work
@@ -512,41 +460,72 @@ static const float* tp(const float* const* t, const std::string& name) {
   return i < 0 ? nullptr : t[i];
 }
 
-// fold BN (or nothing) into a [cout][cin*ks*ks] weight and bias
-static void fold(const float* const* t, const std::string& conv, const std::string& bn, int cout,
-                 int per, bool has_bias, std::vector<float>& w, std::vector<float>& b) {
+// Fold BN (or nothing) into conv `conv` ([cout][cin][ks][ks]) and zero-pad to [cout_p][cin_p].
+static Folded folded_padded(const float* const* t, const std::string& conv, const std::string& bn,
+                            int cout, int cin, int ks, bool has_bias, int cout_p, int cin_p) {
   const float* cw = tp(t, conv + ".weight");
   const float* cb = has_bias ? tp(t, conv + ".bias") : nullptr;
-  w.resize((size_t)cout * per);
-  b.resize(cout);
+  Folded f;
+  f.cout = cout_p; f.cin = cin_p; f.ks = ks;
+  f.w.assign((size_t)cout_p * cin_p * ks * ks, 0.f);
+  f.b.assign(cout_p, 0.f);
   for (int co = 0; co < cout; ++co) {
     float scale = 1.f, shift = 0.f;
     if (!bn.empty()) {
       scale = tp(t, bn + ".weight")[co] / std::sqrt(tp(t, bn + ".running_var")[co] + 1e-5f);
       shift = tp(t, bn + ".bias")[co] - tp(t, bn + ".running_mean")[co] * scale;
     }
-    for (int i = 0; i < per; ++i) w[(size_t)co * per + i] = cw[(size_t)co * per + i] * scale;
-    b[co] = (cb ? cb[co] * scale : 0.f) + shift;
+    for (int ci = 0; ci < cin; ++ci)
+      for (int k = 0; k < ks * ks; ++k)
+        f.w[((size_t)co * cin_p + ci) * ks * ks + k] = cw[((size_t)co * cin + ci) * ks * ks + k] * scale;
+    f.b[co] = (cb ? cb[co] * scale : 0.f) + shift;
   }
+  return f;
+}
+
+static int add_tail_conv(umt_model* m, const Folded& f, bool relu, bool residual) {
+  ConvLayer L;
+  L.cout = f.cout; L.cin = f.cin; L.stride = 1; L.geom = 3; L.relu = relu ? 1 : 0;
+  L.res_buf = residual ? 0 : -1;   // only "has a residual" matters here; tensors are bound per call
+  UMT_TRY(build_conv(m, L, f, nullptr));
+  m->tail_convs.push_back(L);
+  return UMT_OK;
 }
 
 int tail_build(umt_model* m, const float* const* t) {
-  std::vector<float> w, b;
+  m->tail_convs.clear();
   const std::string fu = "_feature_extractor._multi_view_fusion.";
-  const int fcin[3] = {144, 108, 72}, fcout[3] = {108, 72, 72};
-  const char* fconv[3] = {"0", "3", "6"};
-  const char* fbn[3] = {"1", "4", ""};
-  for (int i = 0; i < 3; ++i) {
-    fold(t, fu + fconv[i], fbn[i][0] ? fu + fbn[i] : std::string(), fcout[i], fcin[i], true, w, b);
-    m->tw.fus_w[i] = upload(m, w);
-    m->tw.fus_b[i] = upload(m, b);
-  }
+  // fusion: 144 -> 108 (pad 112) -> 72 (pad 80) -> 72 (pad 80)   (model_utils.py:141-163)
+  UMT_TRY(add_tail_conv(m, folded_padded(t, fu + "0", fu + "1", 108, 144, 1, true, 112, 144), true, false));
+  UMT_TRY(add_tail_conv(m, folded_padded(t, fu + "3", fu + "4", 72, 108, 1, true, 80, 112), true, false));
+  UMT_TRY(add_tail_conv(m, folded_padded(t, fu + "6", "", 72, 72, 1, true, 80, 80), false, false));
+  // temporal: three 90 -> 90 (pad 96), ReLU after the first two (temporal.py:31-38)
   const std::string te = "_temporal._temporal_module.";
-  const char* tconv[3] = {"0", "2", "4"};
-  for (int i = 0; i < 3; ++i) {
-    fold(t, te + tconv[i], "", 90, 90, true, w, b);
-    m->tw.tmp_w[i] = upload(m, w);
-    m->tw.tmp_b[i] = upload(m, b);
+  UMT_TRY(add_tail_conv(m, folded_padded(t, te + "0", "", 90, 90, 1, true, 96, 96), true, false));
+  UMT_TRY(add_tail_conv(m, folded_padded(t, te + "2", "", 90, 90, 1, true, 96, 96), true, false));
+  UMT_TRY(add_tail_conv(m, folded_padded(t, te + "4", "", 90, 90, 1, true, 96, 96), false, false));
+  // regressors: two BasicBlocks each (model_utils.py:195-208), C = 76 / 72 padded to 80
+  const char* heads[2] = {"_regressor_k", "_regressor_u"};
+  const int hc[2] = {76, 72}, hout[2] = {62, 63};
+  std::vector<float> w, b;
+  for (int h = 0; h < 2; ++h) {
+    const std::string p = std::string(heads[h]) + "._pose_regression_layers.";
+    for (int blk = 0; blk < 2; ++blk) {
+      const std::string pre = p + std::to_string(blk);
+      UMT_TRY(add_tail_conv(m, folded_padded(t, pre + ".conv1", pre + ".bn1", hc[h], hc[h], 3, false, 80, 80), true, false));
+      UMT_TRY(add_tail_conv(m, folded_padded(t, pre + ".conv2", pre + ".bn2", hc[h], hc[h], 3, false, 80, 80), true, true));
+    }
+    // 1x1 head conv applied after the average pool: [n_out][80] with zero columns for the padding
+    const float* cw = tp(t, p + "2.weight");
+    const float* cb = tp(t, p + "2.bias");
+    w.assign((size_t)hout[h] * 80, 0.f);
+    b.assign(hout[h], 0.f);
+    for (int o = 0; o < hout[h]; ++o) {
+      for (int c = 0; c < hc[h]; ++c) w[(size_t)o * 80 + c] = cw[(size_t)o * hc[h] + c];
+      b[o] = cb[o];
+    }
+    m->tw.head_w[h] = upload(m, w);
+    m->tw.head_b[h] = upload(m, b);
   }
   {  // Linear(132->144) then BN2d(4) over view(4,6,6): channel of output o is o / 36
     const float* lw = tp(t, "_skeleton_enc._layers.0.weight");
@@ -564,21 +543,25 @@ int tail_build(umt_model* m, const float* const* t) {
     m->tw.skel_w = upload(m, w);
     m->tw.skel_b = upload(m, b);
   }
-  const char* heads[2] = {"_regressor_k", "_regressor_u"};
-  const int hc[2] = {76, 72}, hout[2] = {62, 63};
-  for (int h = 0; h < 2; ++h) {
-    const std::string p = std::string(heads[h]) + "._pose_regression_layers.";
-    for (int blk = 0; blk < 2; ++blk)
-      for (int c = 0; c < 2; ++c) {
-        const std::string pre = p + std::to_string(blk);
-        fold(t, pre + (c ? ".conv2" : ".conv1"), pre + (c ? ".bn2" : ".bn1"), hc[h], hc[h] * 9, false, w, b);
-        m->tw.reg_w[h][blk * 2 + c] = upload(m, w);
-        m->tw.reg_b[h][blk * 2 + c] = upload(m, b);
-      }
-    fold(t, p + "2", "", hout[h], hc[h], true, w, b);
-    m->tw.head_w[h] = upload(m, w);
-    m->tw.head_b[h] = upload(m, b);
-  }
+  if (!m->tw.skel_w || !m->tw.skel_b || !m->tw.head_w[0] || !m->tw.head_w[1]) return UMT_ERR_CUDA;
+  return UMT_OK;
+}
+
+// run tail convolution `idx` from `src` to `dst` (residual `res` if the layer has one)
+static int run_tail_conv(umt_model* m, int idx, const FlatTensor& src, const FlatTensor& dst,
+                         const FlatTensor* res, int n_samples, cudaStream_t st) {
+  const ConvLayer& L = m->tail_convs[idx];
+  ConvParams p = L.prog;
+  p.src[0] = src;
+  if (res) p.src[2] = *res;
+  p.out[0] = dst;
+  p.res.base = nullptr;
+  p.weights = L.d_weights;
+  p.bias = L.d_bias;
+  p.n_pos = n_samples * kPos;
+  finalize_conv_params(p, L, /*split=*/true);
+  UMT_TRY(launch_conv(p, L.cout, true, st));
+  ++m->launches;
   return UMT_OK;
 }
 
@@ -590,43 +573,40 @@ int tail_forward(umt_model* m, int head, const float* feats, const float* intrin
                  float* out_scale, float* out_sigma, cudaStream_t st) {
   (void)n_img;
   const int B = n_samples;
-  const int stride = 144 * kPix;
-  float *A = m->tail_a, *Bf = m->tail_b, *Cf = m->tail_c;
+  const FlatTensor &T0 = m->tail_flat[0], &T1 = m->tail_flat[1], &T2 = m->tail_flat[2];
   const TailWeights& tw = m->tw;
-  fuse_prepare_kernel<<<B, 128, 0, st>>>(feats, intrinsics, extrinsics, sample_range, A);
+  fuse_prepare_kernel<<<B, 128, 0, st>>>(feats, intrinsics, extrinsics, sample_range, T0);
   UMT_TRY(check_launch("fuse_prepare_kernel"));
-  UMT_TRY(launch_conv6<1>(A, stride, 144, tw.fus_w[0], tw.fus_b[0], nullptr, 0, Bf, stride, 108, 1, B, st));
-  UMT_TRY(launch_conv6<1>(Bf, stride, 108, tw.fus_w[1], tw.fus_b[1], nullptr, 0, Cf, stride, 72, 1, B, st));
-  UMT_TRY(launch_conv6<1>(Cf, stride, 72, tw.fus_w[2], tw.fus_b[2], nullptr, 0, A, stride, 72, 0, B, st));
-  temporal_prepare_kernel<<<B, 128, 0, st>>>(A, feats, intrinsics, extrinsics, sample_range, memory_idx,
-                                             use_memory, mem_state, prev_extr, n_slots, Bf);
+  UMT_TRY(run_tail_conv(m, 0, T0, T1, nullptr, B, st));
+  UMT_TRY(run_tail_conv(m, 1, T1, T2, nullptr, B, st));
+  UMT_TRY(run_tail_conv(m, 2, T2, T0, nullptr, B, st));
+  temporal_prepare_kernel<<<B, 128, 0, st>>>(T0, feats, intrinsics, extrinsics, sample_range, memory_idx,
+                                             use_memory, mem_state, prev_extr, n_slots, T1);
   UMT_TRY(check_launch("temporal_prepare_kernel"));
-  UMT_TRY(launch_conv6<1>(Bf, stride, 90, tw.tmp_w[0], tw.tmp_b[0], nullptr, 0, Cf, stride, 90, 1, B, st));
-  UMT_TRY(launch_conv6<1>(Cf, stride, 90, tw.tmp_w[1], tw.tmp_b[1], nullptr, 0, A, stride, 90, 1, B, st));
-  UMT_TRY(launch_conv6<1>(A, stride, 90, tw.tmp_w[2], tw.tmp_b[2], nullptr, 0, Bf, stride, 90, 0, B, st));
-  m->launches += 8;
+  UMT_TRY(run_tail_conv(m, 3, T1, T2, nullptr, B, st));
+  UMT_TRY(run_tail_conv(m, 4, T2, T0, nullptr, B, st));
+  UMT_TRY(run_tail_conv(m, 5, T0, T1, nullptr, B, st));
+  m->launches += 2;
   const float* skel = nullptr;
-  int C = 72;
   if (head == UMT_HEAD_KNOWN_SKELETON) {
     skeleton_kernel<<<n_skel, 144, 0, st>>>(skel_axes, skel_rest, tw.skel_w, tw.skel_b, m->tail_skel);
     UMT_TRY(check_launch("skeleton_kernel"));
     ++m->launches;
     skel = m->tail_skel;
-    C = 76;
   }
-  temporal_finish_kernel<<<B, 128, 0, st>>>(Bf, memory_idx, mem_state, n_slots, skel, n_skel, Cf);
+  temporal_finish_kernel<<<B, 128, 0, st>>>(T1, memory_idx, mem_state, n_slots, skel, n_skel, T2);
   UMT_TRY(check_launch("temporal_finish_kernel"));
-  // two BasicBlocks (backbone_resnet.py:56-72): x=Cf -> A -> Bf(+Cf) -> A -> Cf(+Bf)
-  const int h = head;
-  UMT_TRY(launch_conv6<3>(Cf, stride, C, tw.reg_w[h][0], tw.reg_b[h][0], nullptr, 0, A, stride, C, 1, B, st));
-  UMT_TRY(launch_conv6<3>(A, stride, C, tw.reg_w[h][1], tw.reg_b[h][1], Cf, stride, Bf, stride, C, 1, B, st));
-  UMT_TRY(launch_conv6<3>(Bf, stride, C, tw.reg_w[h][2], tw.reg_b[h][2], nullptr, 0, A, stride, C, 1, B, st));
-  UMT_TRY(launch_conv6<3>(A, stride, C, tw.reg_w[h][3], tw.reg_b[h][3], Bf, stride, Cf, stride, C, 1, B, st));
-  head_kernel<<<B, 128, 0, st>>>(Cf, C, tw.head_w[h], tw.head_b[h], head == UMT_HEAD_KNOWN_SKELETON ? 62 : 63,
+  // two BasicBlocks (backbone_resnet.py:56-72): x=T2 -> T0 -> T1(+T2) -> T0 -> T2(+T1)
+  const int c0 = 6 + 4 * head;
+  UMT_TRY(run_tail_conv(m, c0 + 0, T2, T0, nullptr, B, st));
+  UMT_TRY(run_tail_conv(m, c0 + 1, T0, T1, &T2, B, st));
+  UMT_TRY(run_tail_conv(m, c0 + 2, T1, T0, nullptr, B, st));
+  UMT_TRY(run_tail_conv(m, c0 + 3, T0, T2, &T1, B, st));
+  head_kernel<<<B, 128, 0, st>>>(T2, 80, tw.head_w[head], tw.head_b[head], head == UMT_HEAD_KNOWN_SKELETON ? 62 : 63,
                                  head == UMT_HEAD_UNKNOWN_SKELETON ? 1 : 0, extrinsics, sample_range,
                                  hand_idx, out_joint_angles, out_wrist, out_scale, out_sigma);
   UMT_TRY(check_launch("head_kernel"));
-  m->launches += 6;
+  m->launches += 2;
   return UMT_OK;
 }
 
