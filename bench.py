@@ -223,8 +223,13 @@ def main():
         device_step(fd, desc)
     launches = model.last_launch_count + 2
 
-    def timed(fn):
-        barrier()
+    def timed(fn, collective=True):
+        """K steps between CUDA events; with `collective`, bracketed by barriers and reduced to the
+        max over ranks (every rank must call it); without, a purely local measurement."""
+        if collective:
+            barrier()
+        else:
+            torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(K):
@@ -232,11 +237,12 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
-        if world > 1:
+        if collective and world > 1:
             t = torch.tensor([ms], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        barrier()
+        if collective:
+            barrier()
         return ms
 
     sampler = ClockSampler(local_rank)
@@ -323,11 +329,11 @@ def main():
         mem_a = model._mem_features.clone()
         model.set_mode(other)
         device_step(fd, desc)
-        ms_o = timed(lambda: device_step(fd, desc))
+        ms_o = timed(lambda: device_step(fd, desc), collective=False)   # rank 0 only: no collectives here
         model._mem_features.copy_(mem_a)
         kp_b = device_step(fd, desc)
         model.set_mode(args.mode)
-        line["other_mode"] = {"numeric_mode": other, "value": world * B * K / (ms_o * 1e-3), "unit": UNIT,
+        line["other_mode"] = {"numeric_mode": other, "value": B * K / (ms_o * 1e-3), "unit": UNIT, "n_gpus": 1,
                               "keypoint_delta_mm_max": float((kp_a - kp_b).abs().max()),
                               "keypoint_delta_mm_mean": float((kp_a - kp_b).abs().mean())}
         if world == 1 and not args.no_cpu_baseline:

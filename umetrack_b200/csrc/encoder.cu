@@ -95,8 +95,8 @@ __device__ __forceinline__ void tc_commit_multicast(uint32_t bar, uint16_t cta_m
       : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
 }
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred = 0;
@@ -118,14 +118,51 @@ __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                : "memory");
 }
+template <bool TWO = false>
 __device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
                                             uint32_t idesc, uint32_t accumulate) {
+  if (TWO) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void tc_commit2_multicast(uint32_t bar, uint16_t cta_mask) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"(cta_mask)
       : "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `target_rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t target_rank) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(bar), "r"(target_rank)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
 }
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t* v) {
   asm volatile(
@@ -175,7 +212,44 @@ __device__ __forceinline__ OutPos map_output(long long q, int H, int W, int n_po
 // ------------------------------------------------------------------------------------------
 // The implicit-GEMM convolution kernel
 // ------------------------------------------------------------------------------------------
-constexpr int kConvThreads = 256;
+constexpr int kConvThreads = 256;   // 4 control warps + 4 epilogue warps
+
+__device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) {
+  return ((uint64_t)hi << 32) | (uint64_t)lo;
+}
+
+// Issue the MMAs of `n` consecutive taps (one weight stage) for all S sub-tiles.  Descriptors are
+// advanced by adding to their low word: +shift rows for a tap, +128 (2048 B) per sub-tile, +slab
+// bytes per tap on the weight side; everything else is loop invariant.
+template <int S, int COUT, bool SPLIT, bool TWO = false>
+__device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t0, int n, uint32_t a_lo32,
+                                           uint32_t a_hi32, uint32_t a_plane_bytes, uint32_t b_lo32,
+                                           uint32_t b_hi32, uint32_t d_base, uint32_t idesc, uint32_t any,
+                                           bool skip_hilo) {
+  constexpr uint32_t kBHalf16 = (2u * (TWO ? COUT / 2 : COUT) * 16u) >> 4;
+  constexpr uint32_t kBSlab16 = SPLIT ? 2u * kBHalf16 : kBHalf16;
+  const uint32_t a_lo_plane16 = (2u * a_plane_bytes) >> 4;
+  const int tap0 = P.st_tap0[stage] + t0;
+#pragma unroll 1
+  for (int j = 0; j < n; ++j) {
+    const uint32_t shift16 = (uint32_t)((int)P.tap_shift[tap0 + j] - P.lo_shift);   // rows == 16-byte units
+    const uint32_t a0 = a_lo32 + shift16;
+    const uint64_t b_hi = desc64(b_lo32 + (uint32_t)j * kBSlab16, b_hi32);
+    const uint64_t b_lo = desc64(b_lo32 + (uint32_t)j * kBSlab16 + kBHalf16, b_hi32);
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      const uint64_t a_hi = desc64(a0 + (uint32_t)s * 128u, a_hi32);
+      const uint32_t d = d_base + (uint32_t)(s * COUT);
+      tc_mma_bf16<TWO>(d, a_hi, b_hi, idesc, any);
+      if (SPLIT) {
+        const uint64_t a_lo = desc64(a0 + (uint32_t)s * 128u + a_lo_plane16, a_hi32);
+        if (!skip_hilo) tc_mma_bf16<TWO>(d, a_hi, b_lo, idesc, 1u);
+        tc_mma_bf16<TWO>(d, a_lo, b_hi, idesc, 1u);
+      }
+    }
+    any = 1u;
+  }
+}
 
 // Persistent, warp-specialised kernel.  Each CTA (one per SM) walks tiles t = blockIdx.x,
 // blockIdx.x + gridDim.x, ...; a tile is S sub-tiles of 128 positions x all Cout channels.
@@ -185,7 +259,7 @@ constexpr int kConvThreads = 256;
 // tile -- are fetched from L2 once per cluster: each CTA loads 1/cluster of a slab and multicasts
 // it into the shared memory of all CTAs of the cluster.
 template <int COUT, bool SPLIT>
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma_kernel(const __grid_constant__ ConvParams P) {
   extern __shared__ __align__(128) uint8_t smem[];
   // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
@@ -248,6 +322,260 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   if (warp == 0 && lane == 0) {
     // ===== A-patch producer: one 16-channel slice (2 planes hi [+2 planes lo]) per stage =====
     int it = 0;
+    long long w_aempty = 0, t_begin = clock64();
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      const long long q0 = (long long)tile * mc;
+      for (int i = 0; i < P.n_stages; ++i, ++it) {
+        const int slot = it % n_a;
+        const long long c0 = P.dbg ? clock64() : 0;
+        mbar_wait(a_empty(slot), ((uint32_t)(it / n_a) & 1u) ^ 1u);
+        if (P.dbg) w_aempty += clock64() - c0;
+        mbar_expect_tx(a_full(slot), a_stage_bytes);
+        const FlatTensor& T = P.src[P.st_src[i]];
+        const uint8_t* g = T.base + (long long)(2 * P.st_chunk[i]) * T.plane_stride +
+                           ((long long)T.guard + q0 + P.lo_shift) * 16;
+        const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride);
+        bulk_g2s(dst, g, a_plane_bytes, a_full(slot));
+        bulk_g2s(dst + a_plane_bytes, g + T.plane_stride, a_plane_bytes, a_full(slot));
+        if (SPLIT) {
+          bulk_g2s(dst + 2 * a_plane_bytes, g + T.lo_offset, a_plane_bytes, a_full(slot));
+          bulk_g2s(dst + 3 * a_plane_bytes, g + T.lo_offset + T.plane_stride, a_plane_bytes,
+                   a_full(slot));
+        }
+      }
+    }
+    if (P.dbg) { P.dbg[blockIdx.x * 16 + 0] = w_aempty; P.dbg[blockIdx.x * 16 + 1] = clock64() - t_begin; }
+  } else if (warp == 1 && lane == 0) {
+    // ===== weight-slab producer: one (stage, tap) slab per B stage, multicast over the cluster =====
+    // (up to G consecutive taps of one stage travel as one bulk copy; the packed blob of this
+    // numeric mode is contiguous in program order)
+    int kb = 0;
+    long long w_bempty = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      int k = 0;
+      for (int i = 0; i < P.n_stages; ++i) {
+        const int nt = P.st_ntaps[i];
+        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
+          const int n = min(G, nt - t0);
+          const int slot = kb % n_b;
+          const long long c0 = P.dbg ? clock64() : 0;
+          mbar_wait(b_empty(slot), ((uint32_t)(kb / n_b) & 1u) ^ 1u);
+          if (P.dbg) w_bempty += clock64() - c0;
+          const uint32_t bytes = (uint32_t)n * kBSlab;
+          mbar_expect_tx(b_full(slot), bytes);
+          const uint32_t dst = smem_u32(b_base + (size_t)slot * b_stage_bytes);
+          const uint8_t* src = P.weights + (size_t)k * kBSlab;
+          if (cl == 1) {
+            bulk_g2s(dst, src, bytes, b_full(slot));
+          } else {
+            const uint32_t part = bytes / cl;
+            bulk_g2s_multicast(dst + cta_rank * part, src + cta_rank * part, part, b_full(slot), cta_mask);
+          }
+          k += n;
+        }
+      }
+    }
+    if (P.dbg) P.dbg[blockIdx.x * 16 + 2] = w_bempty;
+  } else if (warp == 2) {
+    // ===== MMA issuer: the whole warp walks the program (so every value stays warp-uniform and
+    // lives in uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit =====
+    constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | (1u << 7) /* A = bf16 */ |
+                               (1u << 10) /* B = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
+                               ((128u >> 4) << 24);
+    const bool leader = elect_one();
+    const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
+    const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
+    const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)(((COUT * 16u) >> 4) & 0x3FFF) << 16);
+    int it = 0, kb = 0, tc = 0;
+    long long w_acc = 0, w_a = 0, w_b = 0, t_begin = clock64();
+    unsigned long long g_begin = 0;
+    if (P.dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_begin));
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
+      const int buf = tc % n_buf;
+      long long c0 = P.dbg ? clock64() : 0;
+      mbar_wait(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // epilogue drained this buffer
+      if (P.dbg) w_acc += clock64() - c0;
+      tc_fence_after();
+      const uint32_t d_base = tmem_base + (uint32_t)buf * buf_cols;
+      uint32_t any = 0;
+      for (int i = 0; i < P.n_stages; ++i, ++it) {
+        const int aslot = it % n_a;
+        c0 = P.dbg ? clock64() : 0;
+        mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
+        if (P.dbg) w_a += clock64() - c0;
+        const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
+        const bool skip_hilo = SPLIT && (P.st_flags[i] & 1);   // identity (residual) slabs have w_lo == 0
+        const int nt = P.st_ntaps[i];
+        // low 32 bits of the A descriptors of this stage (start address field, 16-byte units);
+        // tap shift and sub-tile only add to it
+        const uint32_t a_lo32 = (uint32_t)(a_desc_base & 0xFFFFFFFFu) | ((a_s >> 4) & 0x3FFFu);
+        const uint32_t a_hi32 = (uint32_t)(a_desc_base >> 32);
+        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
+          const int n = min(G, nt - t0);
+          const int bslot = kb % n_b;
+          c0 = P.dbg ? clock64() : 0;
+          mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          if (P.dbg) w_b += clock64() - c0;
+          tc_fence_after();
+          const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
+          const uint32_t b_lo32 = (uint32_t)(b_desc_base & 0xFFFFFFFFu) | ((b_s0 >> 4) & 0x3FFFu);
+          const uint32_t b_hi32 = (uint32_t)(b_desc_base >> 32);
+          if (leader) {
+            switch (P.S) {
+              case 1: issue_taps<1, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              case 2: issue_taps<2, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              default: issue_taps<4, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+            }
+            if (cl == 1) tc_commit(b_empty(bslot));
+            else tc_commit_multicast(b_empty(bslot), cta_mask);   // frees the slot in every CTA of the cluster
+          }
+          any = 1u;
+          __syncwarp();
+        }
+        if (leader) tc_commit(a_empty(aslot));
+        __syncwarp();
+      }
+      if (leader) tc_commit(acc_full(buf));
+      __syncwarp();
+    }
+    if (P.dbg && leader) {
+      P.dbg[blockIdx.x * 16 + 3] = w_acc; P.dbg[blockIdx.x * 16 + 4] = w_a; P.dbg[blockIdx.x * 16 + 5] = w_b;
+      P.dbg[blockIdx.x * 16 + 6] = clock64() - t_begin; P.dbg[blockIdx.x * 16 + 7] = tc;
+      unsigned long long g_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_end));
+      unsigned smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      P.dbg[blockIdx.x * 16 + 10] = (long long)g_begin; P.dbg[blockIdx.x * 16 + 11] = (long long)g_end;
+      P.dbg[blockIdx.x * 16 + 12] = smid;
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: TMEM -> registers -> bias / ReLU -> split bf16 -> global =====
+    const int lgrp = warp & 3;  // TMEM lane group this warp may read
+    int tc = 0;
+    long long w_full = 0, t_begin = clock64();
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
+      const int buf = tc % n_buf;
+      const long long c0 = P.dbg ? clock64() : 0;
+      mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
+      if (P.dbg) w_full += clock64() - c0;
+      tc_fence_after();
+      const long long q0 = (long long)tile * mc;
+      for (int s = 0; s < P.S; ++s) {
+        const long long q = q0 + s * 128 + lgrp * 32 + lane;
+        const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
+        const FlatTensor& T = P.out[o.tensor];
+        constexpr int kStep = (COUT % 32 == 0) ? 32 : 16;   // columns per TMEM round trip
+        const float lo_clamp = P.relu ? 0.0f : -INFINITY;
+#pragma unroll 1
+        for (int c0 = 0; c0 < COUT; c0 += kStep) {
+          uint32_t v[kStep];
+          const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) +
+                                 (uint32_t)buf * buf_cols + (uint32_t)(s * COUT + c0);
+          tc_ld16(taddr, v);
+          if (kStep == 32) tc_ld16(taddr + 16, v + 16);
+          tc_ld_wait();
+          if (o.valid) {
+#pragma unroll
+            for (int h = 0; h < kStep / 8; ++h) {
+              float f[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
+              store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty(buf));   // 4 arrivals (one per epilogue warp) free the buffer
+    }
+    if (P.dbg && warp == 4 && lane == 0) { P.dbg[blockIdx.x * 16 + 8] = w_full; P.dbg[blockIdx.x * 16 + 9] = clock64() - t_begin; }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (cl > 1) cluster_sync_all();   // nobody leaves while a peer may still multicast into its smem
+  if (warp == 2) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(tmem_cols)
+                 : "memory");
+  }
+}
+
+// Two-CTA variant (tcgen05 cta_group::2): the CTAs of a cluster pair sit on the two SMs of a TPC;
+// one M=256 MMA, issued by the leader, multiplies 128 positions from EACH CTA's A patch with a
+// weight slab of which each CTA holds only half the output channels.  Per CTA this halves the
+// shared-memory traffic of the weight operand (reads and refills) and the number of MMA
+// instructions.  The peer CTA runs its own producers and epilogue; a relay thread forwards its
+// "stage landed" events to the leader, and the leader's commits are multicast to both CTAs.
+template <int COUT, bool SPLIT>
+__global__ void __launch_bounds__(kConvThreads, 2)
+conv_umma2_kernel(const __grid_constant__ ConvParams P) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 1000);
+  float* s_bias = reinterpret_cast<float*>(smem + 1024);
+  constexpr int kBiasBytes = ((COUT * 4 + 127) / 128) * 128;
+  const int n_a = P.n_a, n_b = P.n_b, n_buf = P.n_buf;
+  const uint32_t a_plane_bytes = (uint32_t)P.patch_rows * 16u;
+  const uint32_t a_stage_bytes = a_plane_bytes * (SPLIT ? 4u : 2u);
+  const uint32_t a_stage_stride = (a_stage_bytes + 127u) & ~127u;
+  constexpr uint32_t kBHalf = 2u * (COUT / 2) * 16u;      // one of {w_hi, w_lo}: 2 planes x Cout/2 rows (this CTA's half of N)
+  constexpr uint32_t kBSlab = SPLIT ? 2u * kBHalf : kBHalf;   // bytes of one (stage, tap) slab in this mode
+  const int G = P.bgroup;                                    // slabs per B pipeline stage
+  const uint32_t b_stage_bytes = (uint32_t)G * kBSlab;
+  uint8_t* a_base = smem + 1024 + kBiasBytes;
+  uint8_t* b_base = a_base + (size_t)n_a * a_stage_stride;
+
+  const uint32_t bar0 = smem_u32(bars);
+  auto a_full = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+  auto a_empty = [&](int i) { return bar0 + 8u * (uint32_t)(n_a + i); };
+  auto b_full = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + i); };
+  auto b_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + n_b + i); };
+  auto acc_full = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + i); };
+  auto acc_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + 2 + i); };
+  // leader only: "the peer CTA's copy of this stage has landed" (one remote arrival per phase)
+  auto a_peer = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + 4 + i); };
+  auto b_peer = [&](int i) { return bar0 + 8u * (uint32_t)(3 * n_a + 2 * n_b + 4 + i); };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t cta_rank = 0;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+  const bool is_leader = (cta_rank == 0);
+  const uint16_t cta_mask = 3;
+  const int mc = P.S * 128;
+  const uint32_t buf_cols = (uint32_t)(P.S * COUT);
+  const uint32_t want_cols = buf_cols * (uint32_t)n_buf;
+  const uint32_t tmem_cols = want_cols <= 32u ? 32u : want_cols <= 64u ? 64u : want_cols <= 128u ? 128u
+                             : want_cols <= 256u ? 256u : 512u;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < n_a; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); mbar_init(a_peer(i), 1); }
+    for (int i = 0; i < n_b; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), 1); mbar_init(b_peer(i), 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(acc_full(i), 1); mbar_init(acc_empty(i), 8); }   // 4 epilogue warps x 2 CTAs
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_slot)),
+                 "r"(tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  if (warp == 3) {
+    for (int c = lane; c < COUT; c += 32) s_bias[c] = P.bias[c];
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // the peer's barriers must be initialised before any remote arrival
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ===== A-patch producer: one 16-channel slice (2 planes hi [+2 planes lo]) per stage =====
+    int it = 0;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       const long long q0 = (long long)tile * mc;
       for (int i = 0; i < P.n_stages; ++i, ++it) {
@@ -283,78 +611,81 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
           const uint32_t bytes = (uint32_t)n * kBSlab;
           mbar_expect_tx(b_full(slot), bytes);
           const uint32_t dst = smem_u32(b_base + (size_t)slot * b_stage_bytes);
-          const uint8_t* src = P.weights + (size_t)k * kBSlab;
-          if (cl == 1) {
-            bulk_g2s(dst, src, bytes, b_full(slot));
-          } else {
-            const uint32_t part = bytes / cl;
-            bulk_g2s_multicast(dst + cta_rank * part, src + cta_rank * part, part, b_full(slot), cta_mask);
-          }
+          // weights are packed per CTA rank: [rank][slab][hi|lo][2 planes][Cout/2][8]
+          const uint8_t* src = P.weights + (size_t)cta_rank * P.w_rank_stride + (size_t)k * kBSlab;
+          bulk_g2s(dst, src, bytes, b_full(slot));
           k += n;
         }
       }
     }
-  } else if (warp == 2) {
-    // ===== MMA issuer: the whole warp walks the program (so every value stays warp-uniform and
+  } else if (warp == 3 && lane == 0 && !is_leader) {
+    // ===== relay (peer CTA only): tell the leader when this CTA's operand stages have landed =====
+    int it = 0, kb = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      for (int i = 0; i < P.n_stages; ++i, ++it) {
+        const int aslot = it % n_a;
+        mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
+        mbar_arrive_remote(a_peer(aslot), 0);
+        const int nt = P.st_ntaps[i];
+        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
+          const int bslot = kb % n_b;
+          mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          mbar_arrive_remote(b_peer(bslot), 0);
+        }
+      }
+    }
+  } else if (warp == 2 && is_leader) {
+    // ===== MMA issuer (leader CTA): the whole warp walks the program (so every value stays warp-uniform and
     // lives in uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit =====
     constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | (1u << 7) /* A = bf16 */ |
                                (1u << 10) /* B = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
-                               ((128u >> 4) << 24);
+                               ((256u >> 4) << 24);   // M = 256: 128 rows from each CTA of the pair
     const bool leader = elect_one();
     const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
     const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
-    const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)(((COUT * 16u) >> 4) & 0x3FFF) << 16);
+    const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)((((COUT / 2) * 16u) >> 4) & 0x3FFF) << 16);
     int it = 0, kb = 0, tc = 0;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
       const int buf = tc % n_buf;
-      mbar_wait(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // epilogue drained this buffer
+      mbar_wait_cluster(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // both epilogues drained this buffer
       tc_fence_after();
       const uint32_t d_base = tmem_base + (uint32_t)buf * buf_cols;
       uint32_t any = 0;
       for (int i = 0; i < P.n_stages; ++i, ++it) {
         const int aslot = it % n_a;
         mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
+        mbar_wait_cluster(a_peer(aslot), (uint32_t)(it / n_a) & 1u);
         const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
         const bool skip_hilo = SPLIT && (P.st_flags[i] & 1);   // identity (residual) slabs have w_lo == 0
         const int nt = P.st_ntaps[i];
+        // low 32 bits of the A descriptors of this stage (start address field, 16-byte units);
+        // tap shift and sub-tile only add to it
+        const uint32_t a_lo32 = (uint32_t)(a_desc_base & 0xFFFFFFFFu) | ((a_s >> 4) & 0x3FFFu);
+        const uint32_t a_hi32 = (uint32_t)(a_desc_base >> 32);
         for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
           const int n = min(G, nt - t0);
           const int bslot = kb % n_b;
           mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          mbar_wait_cluster(b_peer(bslot), (uint32_t)(kb / n_b) & 1u);
           tc_fence_after();
           const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
+          const uint32_t b_lo32 = (uint32_t)(b_desc_base & 0xFFFFFFFFu) | ((b_s0 >> 4) & 0x3FFFu);
+          const uint32_t b_hi32 = (uint32_t)(b_desc_base >> 32);
           if (leader) {
-#pragma unroll 1
-            for (int j = 0; j < n; ++j) {
-              const uint32_t b_s = b_s0 + (uint32_t)j * kBSlab;
-              const uint64_t b_hi = b_desc_base | (uint64_t)((b_s >> 4) & 0x3FFF);
-              const uint64_t b_lo = b_desc_base | (uint64_t)(((b_s + kBHalf) >> 4) & 0x3FFF);
-              const int shift = (int)P.tap_shift[P.st_tap0[i] + t0 + j] - P.lo_shift;
-              const uint32_t a_row0 = a_s + (uint32_t)shift * 16u;
-#pragma unroll 1
-              for (int s = 0; s < P.S; ++s) {
-                const uint32_t a_row = a_row0 + (uint32_t)s * 2048u;
-                const uint64_t a_hi = a_desc_base | (uint64_t)((a_row >> 4) & 0x3FFF);
-                const uint32_t d = d_base + (uint32_t)(s * COUT);
-                tc_mma_bf16(d, a_hi, b_hi, idesc, any);
-                if (SPLIT) {
-                  const uint64_t a_lo = a_desc_base | (uint64_t)(((a_row + 2u * a_plane_bytes) >> 4) & 0x3FFF);
-                  if (!skip_hilo) tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
-                  tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
-                }
-              }
-              any = 1u;
+            switch (P.S) {
+              case 1: issue_taps<1, COUT, SPLIT, true>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              case 2: issue_taps<2, COUT, SPLIT, true>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              default: issue_taps<4, COUT, SPLIT, true>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
             }
-            if (cl == 1) tc_commit(b_empty(bslot));
-            else tc_commit_multicast(b_empty(bslot), cta_mask);   // frees the slot in every CTA of the cluster
+            tc_commit2_multicast(b_empty(bslot), cta_mask);   // frees the slot in both CTAs
           }
           any = 1u;
           __syncwarp();
         }
-        if (leader) tc_commit(a_empty(aslot));
+        if (leader) tc_commit2_multicast(a_empty(aslot), cta_mask);
         __syncwarp();
       }
-      if (leader) tc_commit(acc_full(buf));
+      if (leader) tc_commit2_multicast(acc_full(buf), cta_mask);
       __syncwarp();
     }
   } else if (warp >= 4) {
@@ -394,15 +725,18 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(acc_empty(buf));   // 4 arrivals (one per epilogue warp) free the buffer
+      if (lane == 0) {   // 8 arrivals (4 epilogue warps x 2 CTAs) on the leader's barrier free the buffer
+        if (is_leader) mbar_arrive(acc_empty(buf));
+        else mbar_arrive_remote(acc_empty(buf), 0);
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (cl > 1) cluster_sync_all();   // nobody leaves while a peer may still multicast into its smem
+  cluster_sync_all();   // nobody leaves while the pair still shares barriers / operands
   if (warp == 2) {
     __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
                  "r"(tmem_cols)
                  : "memory");
   }
@@ -411,9 +745,12 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
 static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
   size_t bias = ((size_t)cout * 4 + 127) / 128 * 128;
   size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
-  size_t b = (size_t)2 * cout * 16 * (split ? 2 : 1) * p.bgroup;
+  size_t b = (size_t)2 * (p.two_cta ? cout / 2 : cout) * 16 * (split ? 2 : 1) * p.bgroup;
   return 1024 + bias + a * p.n_a + b * p.n_b;
 }
+
+static long long* g_conv_dbg = nullptr;   // set by umt_debug_set_conv_timeline (tools only)
+void set_conv_debug_buffer(long long* p) { g_conv_dbg = p; }
 
 static int sm_count() {
   static int n = 0;
@@ -428,8 +765,10 @@ static int sm_count() {
 template <int COUT, bool SPLIT>
 static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   const size_t smem = conv_smem_bytes(p, COUT, SPLIT);
-  UMT_CUDA_TRY(cudaFuncSetAttribute(conv_umma_kernel<COUT, SPLIT>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kernel = p.two_cta ? conv_umma2_kernel<COUT, SPLIT> : conv_umma_kernel<COUT, SPLIT>;
+  ConvParams pd = p;
+  pd.dbg = g_conv_dbg;
+  UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = std::min(p.n_tiles, sm_count() * std::max(1, p.occ));
   grid = std::max(p.cluster, grid / p.cluster * p.cluster);
   cudaLaunchConfig_t cfg{};
@@ -444,7 +783,7 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  UMT_CUDA_TRY(cudaLaunchKernelEx(&cfg, conv_umma_kernel<COUT, SPLIT>, p));
+  UMT_CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, pd));
   return check_launch("conv_umma_kernel");
 }
 
@@ -791,10 +1130,13 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
   // (B200 sweep, round 1: two co-resident CTAs per SM beat one larger CTA for every width; as many
   // taps per weight stage as shared memory allows)
   int S = (L.cout == 32) ? 4 : (L.cout == 256 || L.cout % 32 != 0 || L.cout == 96) ? 1 : 2, occ = 2, G = 9, clu = 2, nbuf = 2;
+  int two = 0;
   {
     const std::string name = "UMT_CONV_CFG" + std::to_string(L.cout);
-    if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d,%d,%d,%d", &S, &occ, &G, &clu, &nbuf);
+    if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d,%d,%d,%d,%d", &S, &occ, &G, &clu, &nbuf, &two);
   }
+  p.two_cta = two ? 1 : 0;
+  if (p.two_cta) clu = 2;
   occ = std::max(1, std::min(2, occ));
   while (S > 1 && S * L.cout * occ > 512) S >>= 1;
   p.S = S;
@@ -819,6 +1161,27 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     UMT_CUDA_TRY(cudaMalloc(&L.d_weights_hi, hi.size() * 2));
     m->owned.push_back(L.d_weights_hi);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights_hi, hi.data(), hi.size() * 2, cudaMemcpyHostToDevice));
+  }
+  {  // two-CTA packing: each CTA of a pair holds the weight rows of half the output channels
+    const int hc = L.cout / 2;
+    const size_t half = (size_t)2 * L.cout * 8, part = (size_t)2 * hc * 8;   // elements
+    std::vector<uint16_t> w2((size_t)L.n_slabs * 2 * half), w2h((size_t)L.n_slabs * half);
+    for (int r = 0; r < 2; ++r)
+      for (int k = 0; k < L.n_slabs; ++k)
+        for (int hl = 0; hl < 2; ++hl)
+          for (int pl = 0; pl < 2; ++pl)
+            for (int co = 0; co < hc; ++co)
+              for (int e = 0; e < 8; ++e) {
+                const uint16_t v = blob[(size_t)k * 2 * half + (size_t)hl * half + ((size_t)pl * L.cout + r * hc + co) * 8 + e];
+                w2[((size_t)r * L.n_slabs + k) * 2 * part + (size_t)hl * part + ((size_t)pl * hc + co) * 8 + e] = v;
+                if (hl == 0) w2h[((size_t)r * L.n_slabs + k) * part + ((size_t)pl * hc + co) * 8 + e] = v;
+              }
+    UMT_CUDA_TRY(cudaMalloc(&L.d_weights2, w2.size() * 2));
+    m->owned.push_back(L.d_weights2);
+    UMT_CUDA_TRY(cudaMemcpy(L.d_weights2, w2.data(), w2.size() * 2, cudaMemcpyHostToDevice));
+    UMT_CUDA_TRY(cudaMalloc(&L.d_weights2_hi, w2h.size() * 2));
+    m->owned.push_back(L.d_weights2_hi);
+    UMT_CUDA_TRY(cudaMemcpy(L.d_weights2_hi, w2h.data(), w2h.size() * 2, cudaMemcpyHostToDevice));
   }
   L.d_bias = upload(m, bias);
   if (!L.d_bias) return UMT_ERR_CUDA;
@@ -967,20 +1330,26 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool
   }
   if (L.res_buf >= 0) p.src[2] = m->buf[g][L.res_buf];
   p.res.base = nullptr;
-  p.weights = split ? L.d_weights : L.d_weights_hi;
   p.bias = L.d_bias;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);
   finalize_conv_params(p, L, split);
 }
 
 void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split) {
+  if (p.two_cta) {
+    p.weights = split ? L.d_weights2 : L.d_weights2_hi;
+    p.w_rank_stride = (long long)L.n_slabs * 2 * (L.cout / 2) * 16 * (split ? 2 : 1);
+  } else {
+    p.weights = split ? L.d_weights : L.d_weights_hi;
+    p.w_rank_stride = 0;
+  }
   // pipeline depths from the shared-memory budget
   const int mc = p.S * 128;
   p.n_tiles = ((p.n_pos + mc - 1) / mc + p.cluster - 1) / p.cluster * p.cluster;
   const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 108 : 200) * 1024;
   const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   const size_t fixed = 1024 + ((size_t)L.cout * 4 + 127) / 128 * 128;
-  const size_t slab = (size_t)2 * L.cout * 16 * (split ? 2 : 1);
+  const size_t slab = (size_t)2 * (p.two_cta ? L.cout / 2 : L.cout) * 16 * (split ? 2 : 1);
   while (p.bgroup > 1 && fixed + a * 2 + slab * p.bgroup * 3 > budget) --p.bgroup;   // keep >= 3 B stages
   const size_t b = slab * p.bgroup;
   int n_a = env_int("UMT_CONV_NA", 3);
@@ -1042,7 +1411,9 @@ int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, 
   const size_t dense = (size_t)n_img * L.cout * p.H * p.W * sizeof(float);
   if (out_simt) {
     UMT_CUDA_TRY(cudaMemsetAsync(out_simt, 0, dense, st));
-    conv_simt_check_kernel<<<blocks, 256, 0, st>>>(p, L.cout, split ? 1 : 0, out_simt);
+    ConvParams pc = p;   // the check kernel reads the one-CTA weight packing
+    pc.weights = split ? L.d_weights : L.d_weights_hi;
+    conv_simt_check_kernel<<<blocks, 256, 0, st>>>(pc, L.cout, split ? 1 : 0, out_simt);
     UMT_TRY(check_launch("conv_simt_check_kernel"));
   }
   if (out_umma) {

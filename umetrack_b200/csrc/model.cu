@@ -259,6 +259,10 @@ extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* 
                       n_slots, out_joint_angles, out_wrist, out_scale, out_sigma, st);
 }
 
+// Tools only (not declared in the public header): device buffer [grid][16] of int64 that every
+// later conv launch fills with per-role wait/total cycle counters; nullptr switches it off.
+extern "C" void umt_debug_set_conv_timeline(long long* device_buffer) { set_conv_debug_buffer(device_buffer); }
+
 extern "C" int umt_model_last_launch_count(const umt_model* m) { return m ? m->launches : 0; }
 
 extern "C" int umt_model_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,

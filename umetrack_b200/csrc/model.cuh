@@ -36,6 +36,9 @@ struct ConvParams {
   FlatTensor out[4];        // [0] for flat output; four parity-phase tensors when phase_out
   FlatTensor res;           // unused by the tensor-core kernel (residuals enter as identity-weight K)
   const uint8_t* weights;   // packed operand slabs in program order
+  long long w_rank_stride;  // two-CTA packing: bytes between the two CTA ranks' halves
+  long long* dbg;           // optional [grid][16] cycle counters (tools/conv_timeline.py); nullptr in production
+  int two_cta;              // 1: cta_group::2 kernel (cluster pair shares each MMA)
   const float* bias;        // [COUT]
   int H, W;                 // output-domain geometry
   int n_pos;                // valid positions: n_img * (H+1) * (W+1)
@@ -67,6 +70,8 @@ struct ConvLayer {
   int n_slabs = 0;
   uint8_t* d_weights = nullptr;                   // packed [slab][hi|lo][2][cout][8] bf16
   uint8_t* d_weights_hi = nullptr;                // packed [slab][2][cout][8] bf16 (hi only)
+  uint8_t* d_weights2 = nullptr;                  // two-CTA packing [rank][slab][hi|lo][2][cout/2][8]
+  uint8_t* d_weights2_hi = nullptr;               // two-CTA packing [rank][slab][2][cout/2][8]
   float* d_bias = nullptr;
   ConvParams prog{};                              // program template (tensors filled per call)
 };
@@ -123,6 +128,7 @@ int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, 
                         float* out_simt, float* out_umma, int* shape, cudaStream_t st);
 size_t encoder_workspace_bytes(int chunk_images);
 void encoder_bind(umt_model* m, uint8_t* base);
+void set_conv_debug_buffer(long long* p);
 int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds);
 int launch_conv(const ConvParams& p, int cout, bool split, cudaStream_t st);
 void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split);

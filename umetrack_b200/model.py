@@ -87,7 +87,7 @@ class UmeTrackModel:
     """Inference-only model bound to one CUDA device."""
 
     def __init__(self, state_dict: Dict[str, torch.Tensor], opts: ModelOpts = ModelOpts(),
-                 chunk_images: int = 2048):
+                 chunk_images: int = 4096):
         arch.check_supported(opts)
         validate_state_dict(state_dict)
         self._opts = opts
