@@ -39,6 +39,8 @@ extern "C" {
 /* numeric mode of the encoder convolutions */
 #define UMT_MODE_FP32_EQUIV 0 /* split-bf16 (hi+lo) operands, 3 tensor-core products, fp32 accumulate */
 #define UMT_MODE_BF16 1       /* single bf16 product, fp32 accumulate */
+#define UMT_MODE_FP16 2       /* single fp16 product (11-bit significands), fp32 accumulate; activations and
+                                 BN-folded weights must stay inside the half range (|x| < 65504) */
 
 /* regression head */
 #define UMT_HEAD_KNOWN_SKELETON 0   /* _regressor_k, regress_pose_use_skeleton */

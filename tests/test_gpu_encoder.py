@@ -66,12 +66,15 @@ def test_chunking_and_batch_independence(setup):
     assert torch.equal(one[0], out[4])
 
 
-def test_bf16_mode_reports_its_error(setup):
+def test_reduced_precision_modes_report_their_error(setup):
     sd, model, imgs, _, feats = setup
-    model.set_mode("bf16")
-    try:
-        out = model.encode(imgs).cpu()
-    finally:
-        model.set_mode("fp32")
-    rel = float((out - feats).abs().max()) / float(feats.abs().max())
-    assert 1e-4 < rel < 8e-2, rel   # bf16 really is lower precision, but not garbage
+    rel = {}
+    for mode in ("bf16", "fp16"):
+        model.set_mode(mode)
+        try:
+            out = model.encode(imgs).cpu()
+        finally:
+            model.set_mode("fp32")
+        rel[mode] = float((out - feats).abs().max()) / float(feats.abs().max())
+    assert 1e-4 < rel["bf16"] < 8e-2, rel   # bf16 really is lower precision, but not garbage
+    assert 1e-5 < rel["fp16"] < rel["bf16"] / 3, rel   # 11-bit vs 8-bit significands

@@ -105,3 +105,25 @@ def test_errors_are_loud():
         m.to("cpu")
     with pytest.raises(RuntimeError):
         m.encode(torch.zeros(1, 96, 96))   # no .to('cuda') yet
+
+
+@pytest.mark.parametrize("mode,tol_mm", [("fp16", KEYPOINT_TOL_MM)])
+def test_sixteen_bit_encoder_mode_meets_the_keypoint_gate(mode, tol_mm):
+    """BASELINE configs[3]: 16-bit encoder vs fp32 tolerance check.  fp16 operands (fp32 accumulate)
+    must keep the keypoints inside the same 0.05 mm gate as the fp32-equivalent mode."""
+    sd = synthetic.make_state_dict(0)
+    model = UmeTrackModel(sd).to("cuda").set_mode(mode)
+    orc = O.OracleModel(sd)
+    hm = hmod.load_hand_model_from_dict(hm_dict())
+    ax, rest = hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None]
+    worst = 0.0
+    for step in range(3):
+        b = synthetic.make_model_batch(48, seed=400 + step, single_view_every=5)
+        b["use_memory"][:] = step > 0
+        out = model.regress_pose_use_skeleton(*_inputs(b), InputSkeletonData(ax, rest))
+        ref = orc.regress_pose_use_skeleton(b["left_images"], b["intrinsics"], b["extrinsics_xf"], b["sample_range"],
+                                            b["memory_idx"], b["use_memory"], b["hand_idx"], ax, rest)
+        kp = _keypoints_mm(hm, out.joint_angles.cpu(), out.wrist_xfs.cpu())
+        kp_ref = _keypoints_mm(hm, ref["joint_angles"], ref["wrist_xfs"])
+        worst = max(worst, float((kp - kp_ref).abs().max()))
+    assert worst < tol_mm, f"{mode}: keypoints differ from the oracle by {worst} mm"

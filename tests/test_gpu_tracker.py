@@ -48,3 +48,14 @@ def test_unknown_skeleton_calibration_matches_reference():
     assert np.abs(scales - ref).max() < 1e-4
     assert abs(mean_scale - ref.mean()) < 1e-4
     assert torch.allclose(scaled.joint_rest_positions, generic.joint_rest_positions * mean_scale)
+
+
+def test_known_skeleton_recording_in_fp16_mode_meets_the_gates():
+    g = golden("tracker_golden.npz")
+    labels, frames = synthetic.make_recording(hm_dict(), seed=3, n_frames=12)
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda").set_mode("fp16")
+    res = track_recording(model, labels, frames)
+    assert np.array_equal(res["valid_tracking"], g["valid"])
+    d = np.abs(res["tracked_keypoints"] - g["tracked"])[g["valid"]]
+    assert d.max() < 0.05, f"fp16 keypoints differ by {d.max()} mm"
+    assert abs(res["per_frame_mean_error"].mean() - g["per_frame_error"].mean()) < 0.01

@@ -22,7 +22,7 @@ for li, nb in enumerate((2, 3, 5, 2)):
         names += [None, f"layer{li + 1}.{b}"]
 model = UmeTrackModel(sd).to("cuda")
 bad = False
-for mode in ("fp32", "bf16"):
+for mode in ("fp32", "bf16", "fp16"):
     model.set_mode(mode)
     for layer in range(24):
         simt, umma = model.debug_layer(layer, imgs)

@@ -26,7 +26,7 @@ for cfg in configs:
         os.environ[f"UMT_CONV_CFG{c}"] = cfg
     model = UmeTrackModel(sd).to("cuda")
     row = [f"cfg {cfg:<12}"]
-    for mode in ("fp32", "bf16"):
+    for mode in ("fp32", "bf16", "fp16"):
         model.set_mode(mode)
         try:
             model.profile_layers(imgs)

@@ -71,7 +71,7 @@ int static_scratch_for_current_device(uint8_t** out) {
 extern "C" int umt_model_encode_static(umt_model* m, int mode, const float* images, int n_img,
                                        float* features, void* stream) {
   if (!m) return umt::fail(UMT_ERR_INVALID, "umt_model_encode_static: model is null");
-  if (mode != UMT_MODE_FP32_EQUIV && mode != UMT_MODE_BF16)
+  if (mode < UMT_MODE_FP32_EQUIV || mode > UMT_MODE_FP16)
     return umt::fail(UMT_ERR_INVALID, "umt_model_encode_static: bad mode %d", mode);
   if (n_img < 0) return umt::fail(UMT_ERR_INVALID, "umt_model_encode_static: n_img=%d", n_img);
   if (n_img == 0) return UMT_OK;   // nothing to do, pointers may be null

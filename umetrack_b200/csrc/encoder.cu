@@ -258,9 +258,10 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
 // MMAs of tile i+1.  With a cluster of `cluster` CTAs the weight slabs -- identical for every
 // tile -- are fetched from L2 once per cluster: each CTA loads 1/cluster of a slab and multicasts
 // it into the shared memory of all CTAs of the cluster.
-template <int COUT, bool SPLIT>
+template <int COUT, int MODE>
 __global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma_kernel(const __grid_constant__ ConvParams P) {
+  constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
   extern __shared__ __align__(128) uint8_t smem[];
   // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -379,8 +380,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   } else if (warp == 2) {
     // ===== MMA issuer: the whole warp walks the program (so every value stays warp-uniform and
     // lives in uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit =====
-    constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | (1u << 7) /* A = bf16 */ |
-                               (1u << 10) /* B = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
+    constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 7) /* A */ |
+                               ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 10) /* B: 0 = f16, 1 = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
                                ((128u >> 4) << 24);
     const bool leader = elect_one();
     const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
@@ -481,7 +482,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
 #pragma unroll
               for (int e = 0; e < 8; ++e)
                 f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
-              store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
+              store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
             }
           }
         }
@@ -509,9 +510,10 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
 // shared-memory traffic of the weight operand (reads and refills) and the number of MMA
 // instructions.  The peer CTA runs its own producers and epilogue; a relay thread forwards its
 // "stage landed" events to the leader, and the leader's commits are multicast to both CTAs.
-template <int COUT, bool SPLIT>
+template <int COUT, int MODE>
 __global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma2_kernel(const __grid_constant__ ConvParams P) {
+  constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
   extern __shared__ __align__(128) uint8_t smem[];
   // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -637,8 +639,8 @@ conv_umma2_kernel(const __grid_constant__ ConvParams P) {
   } else if (warp == 2 && is_leader) {
     // ===== MMA issuer (leader CTA): the whole warp walks the program (so every value stays warp-uniform and
     // lives in uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit =====
-    constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | (1u << 7) /* A = bf16 */ |
-                               (1u << 10) /* B = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
+    constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 7) /* A */ |
+                               ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 10) /* B: 0 = f16, 1 = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
                                ((256u >> 4) << 24);   // M = 256: 128 rows from each CTA of the pair
     const bool leader = elect_one();
     const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
@@ -718,7 +720,7 @@ conv_umma2_kernel(const __grid_constant__ ConvParams P) {
 #pragma unroll
               for (int e = 0; e < 8; ++e)
                 f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
-              store_row8<SPLIT>(T, (c0 >> 3) + h, o.row, f);
+              store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
             }
           }
         }
@@ -762,10 +764,10 @@ static int sm_count() {
   return n;
 }
 
-template <int COUT, bool SPLIT>
+template <int COUT, int MODE>
 static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
-  const size_t smem = conv_smem_bytes(p, COUT, SPLIT);
-  auto kernel = p.two_cta ? conv_umma2_kernel<COUT, SPLIT> : conv_umma_kernel<COUT, SPLIT>;
+  const size_t smem = conv_smem_bytes(p, COUT, MODE == UMT_MODE_FP32_EQUIV);
+  auto kernel = p.two_cta ? conv_umma2_kernel<COUT, MODE> : conv_umma_kernel<COUT, MODE>;
   ConvParams pd = p;
   pd.dbg = g_conv_dbg;
   UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -787,25 +789,35 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   return check_launch("conv_umma_kernel");
 }
 
-int launch_conv(const ConvParams& p, int cout, bool split, cudaStream_t st) {
-  switch (cout) {
-    case 32: return split ? launch_conv_t<32, true>(p, st) : launch_conv_t<32, false>(p, st);
-    case 64: return split ? launch_conv_t<64, true>(p, st) : launch_conv_t<64, false>(p, st);
-    case 128: return split ? launch_conv_t<128, true>(p, st) : launch_conv_t<128, false>(p, st);
-    case 256: return split ? launch_conv_t<256, true>(p, st) : launch_conv_t<256, false>(p, st);
-    // widths of the fusion / temporal / regressor layers (always fp32-equivalent)
-    case 80: if (split) return launch_conv_t<80, true>(p, st); break;
-    case 96: if (split) return launch_conv_t<96, true>(p, st); break;
-    case 112: if (split) return launch_conv_t<112, true>(p, st); break;
+template <int COUT>
+static int launch_conv_c(const ConvParams& p, int mode, cudaStream_t st) {
+  switch (mode) {
+    case UMT_MODE_FP32_EQUIV: return launch_conv_t<COUT, UMT_MODE_FP32_EQUIV>(p, st);
+    case UMT_MODE_BF16: return launch_conv_t<COUT, UMT_MODE_BF16>(p, st);
+    case UMT_MODE_FP16: return launch_conv_t<COUT, UMT_MODE_FP16>(p, st);
   }
-  return fail(UMT_ERR_UNSUPPORTED, "conv: unsupported Cout %d (split=%d)", cout, (int)split);
+  return fail(UMT_ERR_INVALID, "conv: bad mode %d", mode);
+}
+
+int launch_conv(const ConvParams& p, int cout, int mode, cudaStream_t st) {
+  switch (cout) {
+    case 32: return launch_conv_c<32>(p, mode, st);
+    case 64: return launch_conv_c<64>(p, mode, st);
+    case 128: return launch_conv_c<128>(p, mode, st);
+    case 256: return launch_conv_c<256>(p, mode, st);
+    // widths of the fusion / temporal / regressor layers (always fp32-equivalent)
+    case 80: if (mode == UMT_MODE_FP32_EQUIV) return launch_conv_t<80, UMT_MODE_FP32_EQUIV>(p, st); break;
+    case 96: if (mode == UMT_MODE_FP32_EQUIV) return launch_conv_t<96, UMT_MODE_FP32_EQUIV>(p, st); break;
+    case 112: if (mode == UMT_MODE_FP32_EQUIV) return launch_conv_t<112, UMT_MODE_FP32_EQUIV>(p, st); break;
+  }
+  return fail(UMT_ERR_UNSUPPORTED, "conv: unsupported Cout %d (mode %d)", cout, mode);
 }
 
 // ------------------------------------------------------------------------------------------
 // CUDA-core check kernel (test hook): same program, same packed weights, plain fp32 FMAs,
 // dense [n, C, H, W] float output.  One thread per (position, output channel).
 // ------------------------------------------------------------------------------------------
-__global__ void conv_simt_check_kernel(const ConvParams P, int cout, int split,
+__global__ void conv_simt_check_kernel(const ConvParams P, int cout, int mode,
                                        float* __restrict__ out /* [n,cout,H,W] */) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int Wp = P.W + 1, S = (P.H + 1) * Wp;
@@ -817,6 +829,7 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int split,
   if (x >= P.W || y >= P.H) return;
   float acc = 0.f;
   int k = 0;
+  const int split = (mode == 0);
   const size_t half = (size_t)2 * cout * 16, slab = split ? 2 * half : half;
   for (int i = 0; i < P.n_stages; ++i) {
     const FlatTensor& T = P.src[P.st_src[i]];
@@ -824,17 +837,15 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int split,
       const long long row = q + P.tap_shift[P.st_tap0[i] + t];
       const uint8_t* w = P.weights + (size_t)k * slab;
       for (int pl = 0; pl < 2; ++pl) {
-        const uint8_t* ap = T.base + (long long)(2 * P.st_chunk[i] + pl) * T.plane_stride +
-                            (T.guard + row) * 16;
-        const __nv_bfloat16* ah = reinterpret_cast<const __nv_bfloat16*>(ap);
-        const __nv_bfloat16* al = reinterpret_cast<const __nv_bfloat16*>(ap + T.lo_offset);
-        const __nv_bfloat16* wh = reinterpret_cast<const __nv_bfloat16*>(w + (size_t)pl * cout * 16 + (size_t)co * 16);
-        const __nv_bfloat16* wl = reinterpret_cast<const __nv_bfloat16*>(w + half + (size_t)pl * cout * 16 + (size_t)co * 16);
+        const uint8_t* wb = w + (size_t)pl * cout * 16 + (size_t)co * 16;
         for (int e = 0; e < 8; ++e) {
-          float a = __bfloat162float(ah[e]), b = __bfloat162float(wh[e]);
-          if (split) {
-            a += __bfloat162float(al[e]);
-            b += __bfloat162float(wl[e]);
+          const float a = load_elem(T, mode, (2 * P.st_chunk[i] + pl) * 8 + e, row);
+          float b;
+          if (mode == 2) {
+            b = __half2float(reinterpret_cast<const __half*>(wb)[e]);
+          } else {
+            b = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(wb)[e]);
+            if (split) b += __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(wb + half)[e]);
           }
           acc = fmaf(a, b, acc);
         }
@@ -842,18 +853,12 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int split,
     }
   }
   acc += P.bias[co];
-  if (P.res.base) {
-    const uint8_t* rp = P.res.base + (long long)(co >> 3) * P.res.plane_stride + (P.res.guard + q) * 16;
-    float r = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rp)[co & 7]);
-    if (split) r += __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rp + P.res.lo_offset)[co & 7]);
-    acc += r;
-  }
-  acc = fmaxf(acc, 0.f);
+  if (P.relu) acc = fmaxf(acc, 0.f);
   out[(((size_t)img * cout + co) * P.H + y) * P.W + x] = acc;
 }
 
 // planar flat (or 4 parity-phase tensors) -> dense [n, C, H, W] float (test hook)
-__global__ void densify_kernel(const ConvParams P, int C, int split, float* __restrict__ out) {
+__global__ void densify_kernel(const ConvParams P, int C, int mode, float* __restrict__ out) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long total = (long long)P.n_pos * C;
   if (idx >= total) return;
@@ -862,9 +867,7 @@ __global__ void densify_kernel(const ConvParams P, int C, int split, float* __re
   const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
   if (!o.valid) return;
   const FlatTensor& T = P.out[o.tensor];
-  const uint8_t* p = T.base + (long long)(c >> 3) * T.plane_stride + (T.guard + o.row) * 16;
-  float v = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[c & 7]);
-  if (split) v += __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p + T.lo_offset)[c & 7]);
+  const float v = load_elem(T, mode, c, o.row);
   const int Wp = P.W + 1, S = (P.H + 1) * Wp;
   const int img = (int)(q / S), rem = (int)(q % S), y = rem / Wp, x = rem % Wp;
   out[(((size_t)img * C + c) * P.H + y) * P.W + x] = v;
@@ -874,7 +877,7 @@ __global__ void densify_kernel(const ConvParams P, int C, int split, float* __re
 // Stem: conv3x3(1->32, bias) + BN + ReLU + MaxPool2 (lib/models/model_utils.py:119-124), BN folded.
 // One thread per pooled output pixel; writes the 32 channels as four 16-byte rows (hi [+ lo]).
 // ------------------------------------------------------------------------------------------
-template <bool SPLIT>
+template <int MODE>
 __global__ void __launch_bounds__(256)
 stem_kernel(const float* __restrict__ images, int n_img, const float* __restrict__ w /* [32][9] */,
             const float* __restrict__ b, FlatTensor out) {
@@ -919,7 +922,7 @@ stem_kernel(const float* __restrict__ images, int n_img, const float* __restrict
       }
       v[e] = best;
     }
-    store_row8<SPLIT>(out, g, row, v);
+    store_row8<MODE>(out, g, row, v);
   }
 }
 
@@ -928,7 +931,7 @@ stem_kernel(const float* __restrict__ images, int n_img, const float* __restrict
 // dense float32 [n,72,6,6].  One CTA per image: activations in shared memory, each thread
 // produces one output channel for six pixels (weights read once per six FMAs).
 // ------------------------------------------------------------------------------------------
-template <bool SPLIT>
+template <int MODE>
 __global__ void __launch_bounds__(432)
 proj_kernel(FlatTensor in, int n_img, const float* __restrict__ w /* [256][72], transposed */,
             const float* __restrict__ b, float* __restrict__ out) {
@@ -938,7 +941,7 @@ proj_kernel(FlatTensor in, int n_img, const float* __restrict__ w /* [256][72], 
     const int pix = i / 32, plane = i % 32;
     const long long row = (long long)img * 49 + (pix / 6) * 7 + (pix % 6);
     float v[8];
-    load_row8<SPLIT>(in, plane, row, v);
+    load_row8<MODE>(in, plane, row, v);
 #pragma unroll
     for (int e = 0; e < 8; ++e) sx[pix][plane * 8 + e] = v[e];
   }
@@ -965,6 +968,22 @@ static inline uint16_t f2bf(float f) {  // round to nearest even
   if ((u & 0x7F800000u) == 0x7F800000u) return (uint16_t)(u >> 16);
   u += 0x7FFFu + ((u >> 16) & 1u);
   return (uint16_t)(u >> 16);
+}
+static inline uint16_t f2h(float f) {  // float -> IEEE half, round to nearest even, saturating
+  uint32_t x;
+  memcpy(&x, &f, 4);
+  const uint32_t sign = (x >> 16) & 0x8000u;
+  x &= 0x7FFFFFFFu;
+  if (x >= 0x47800000u) return (uint16_t)(sign | (x > 0x7F800000u ? 0x7E00u : 0x7BFFu));   // NaN / clamp to 65504
+  if (x < 0x38800000u) {  // subnormal half or zero
+    if (x < 0x33000000u) return (uint16_t)sign;
+    const int shift = 126 - (int)(x >> 23);          // 14..24
+    uint32_t mant = (x & 0x7FFFFFu) | 0x800000u;
+    const uint32_t rounded = (mant + (1u << (shift - 1)) - 1u + ((mant >> shift) & 1u)) >> shift;
+    return (uint16_t)(sign | rounded);
+  }
+  const uint32_t r = x + 0xFFFu + ((x >> 13) & 1u);   // round mantissa to 10 bits
+  return (uint16_t)(sign | ((r - 0x38000000u) >> 13));
 }
 static inline float bf2f(uint16_t h) {
   uint32_t u = (uint32_t)h << 16;
@@ -1183,6 +1202,28 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     m->owned.push_back(L.d_weights2_hi);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights2_hi, w2h.data(), w2h.size() * 2, cudaMemcpyHostToDevice));
   }
+  {  // fp16 weights (UMT_MODE_FP16), both packings.  Values beyond the half range saturate.
+    const int hc = L.cout / 2;
+    const size_t half = (size_t)2 * L.cout * 8, part = (size_t)2 * hc * 8;
+    std::vector<uint16_t> h1((size_t)L.n_slabs * half), h2((size_t)L.n_slabs * half);
+    for (int k = 0; k < L.n_slabs; ++k)
+      for (int pl = 0; pl < 2; ++pl)
+        for (int co = 0; co < L.cout; ++co)
+          for (int e = 0; e < 8; ++e) {
+            const size_t src = (size_t)k * 2 * half + ((size_t)pl * L.cout + co) * 8 + e;
+            const float v = bf2f(blob[src]) + bf2f(blob[src + half]);   // hi + lo == the folded fp32 weight (to 2^-17)
+            const uint16_t hv = f2h(v);
+            h1[(size_t)k * half + ((size_t)pl * L.cout + co) * 8 + e] = hv;
+            const int r = co / hc, cr = co % hc;
+            h2[((size_t)r * L.n_slabs + k) * part + ((size_t)pl * hc + cr) * 8 + e] = hv;
+          }
+    UMT_CUDA_TRY(cudaMalloc(&L.d_weights_h16, h1.size() * 2));
+    m->owned.push_back(L.d_weights_h16);
+    UMT_CUDA_TRY(cudaMemcpy(L.d_weights_h16, h1.data(), h1.size() * 2, cudaMemcpyHostToDevice));
+    UMT_CUDA_TRY(cudaMalloc(&L.d_weights2_h16, h2.size() * 2));
+    m->owned.push_back(L.d_weights2_h16);
+    UMT_CUDA_TRY(cudaMemcpy(L.d_weights2_h16, h2.data(), h2.size() * 2, cudaMemcpyHostToDevice));
+  }
   L.d_bias = upload(m, bias);
   if (!L.d_bias) return UMT_ERR_CUDA;
   return UMT_OK;
@@ -1311,9 +1352,9 @@ void encoder_bind(umt_model* m, uint8_t* base) {
 }
 
 // pipeline depths etc. once tensors, weights and n_pos are known
-void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split);
+void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode);
 
-static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool split,
+static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, int mode,
                          ConvParams& p) {
   p = L.prog;
   const int g = L.geom;
@@ -1332,15 +1373,16 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, bool
   p.res.base = nullptr;
   p.bias = L.d_bias;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);
-  finalize_conv_params(p, L, split);
+  finalize_conv_params(p, L, mode);
 }
 
-void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split) {
+void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
+  const bool split = (mode == UMT_MODE_FP32_EQUIV);
   if (p.two_cta) {
-    p.weights = split ? L.d_weights2 : L.d_weights2_hi;
+    p.weights = split ? L.d_weights2 : (mode == UMT_MODE_FP16 ? L.d_weights2_h16 : L.d_weights2_hi);
     p.w_rank_stride = (long long)L.n_slabs * 2 * (L.cout / 2) * 16 * (split ? 2 : 1);
   } else {
-    p.weights = split ? L.d_weights : L.d_weights_hi;
+    p.weights = split ? L.d_weights : (mode == UMT_MODE_FP16 ? L.d_weights_h16 : L.d_weights_hi);
     p.w_rank_stride = 0;
   }
   // pipeline depths from the shared-memory budget
@@ -1364,31 +1406,34 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
   if (!m->ws) return fail(UMT_ERR_INVALID, "no workspace bound (umt_model_bind_workspace)");
   if (n_img <= 0 || n_img > m->chunk_images)
     return fail(UMT_ERR_INVALID, "encoder chunk of %d images (capacity %d)", n_img, m->chunk_images);
-  const bool split = (mode == UMT_MODE_FP32_EQUIV);
   const long long px = (long long)n_img * 2304;
   const int blocks = (int)((px + 255) / 256);
   if (ev) cudaEventRecord(ev[0], st);
-  if (split)
-    stem_kernel<true><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
+  if (mode == UMT_MODE_FP32_EQUIV)
+    stem_kernel<UMT_MODE_FP32_EQUIV><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
+  else if (mode == UMT_MODE_BF16)
+    stem_kernel<UMT_MODE_BF16><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
   else
-    stem_kernel<false><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
+    stem_kernel<UMT_MODE_FP16><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
   UMT_TRY(check_launch("stem_kernel"));
   ++m->launches;
   for (size_t i = 0; i < m->convs.size(); ++i) {
     if (stop_after_layer >= 0 && (int)i > stop_after_layer) return UMT_OK;
     ConvParams p;
-    fill_tensors(m, m->convs[i], n_img, split, p);
+    fill_tensors(m, m->convs[i], n_img, mode, p);
     if (ev) cudaEventRecord(ev[1 + i], st);
-    UMT_TRY(launch_conv(p, m->convs[i].cout, split, st));
+    UMT_TRY(launch_conv(p, m->convs[i].cout, mode, st));
     ++m->launches;
   }
   if (ev) cudaEventRecord(ev[1 + m->convs.size()], st);
   if (features) {
     const ConvLayer& last = m->convs.back();
-    if (split)
-      proj_kernel<true><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);
+    if (mode == UMT_MODE_FP32_EQUIV)
+      proj_kernel<UMT_MODE_FP32_EQUIV><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);
+    else if (mode == UMT_MODE_BF16)
+      proj_kernel<UMT_MODE_BF16><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);
     else
-      proj_kernel<false><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);
+      proj_kernel<UMT_MODE_FP16><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);
     UMT_TRY(check_launch("proj_kernel"));
     ++m->launches;
   }
@@ -1399,12 +1444,11 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
 int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
                         float* out_simt, float* out_umma, int* shape, cudaStream_t st) {
   if (layer < 0 || layer >= (int)m->convs.size()) return fail(UMT_ERR_INVALID, "layer %d out of range", layer);
-  const bool split = (mode == UMT_MODE_FP32_EQUIV);
   // inputs of `layer`: run everything before it
   UMT_TRY(encoder_run_chunk(m, mode, images, n_img, nullptr, layer - 1, st, nullptr));
   const ConvLayer& L = m->convs[layer];
   ConvParams p;
-  fill_tensors(m, L, n_img, split, p);
+  fill_tensors(m, L, n_img, mode, p);
   if (shape) { shape[0] = L.cout; shape[1] = p.H; shape[2] = p.W; }
   const long long total = (long long)p.n_pos * L.cout;
   const int blocks = (int)((total + 255) / 256);
@@ -1412,14 +1456,14 @@ int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, 
   if (out_simt) {
     UMT_CUDA_TRY(cudaMemsetAsync(out_simt, 0, dense, st));
     ConvParams pc = p;   // the check kernel reads the one-CTA weight packing
-    pc.weights = split ? L.d_weights : L.d_weights_hi;
-    conv_simt_check_kernel<<<blocks, 256, 0, st>>>(pc, L.cout, split ? 1 : 0, out_simt);
+    pc.weights = mode == UMT_MODE_FP32_EQUIV ? L.d_weights : (mode == UMT_MODE_FP16 ? L.d_weights_h16 : L.d_weights_hi);
+    conv_simt_check_kernel<<<blocks, 256, 0, st>>>(pc, L.cout, mode, out_simt);
     UMT_TRY(check_launch("conv_simt_check_kernel"));
   }
   if (out_umma) {
-    UMT_TRY(launch_conv(p, L.cout, split, st));
+    UMT_TRY(launch_conv(p, L.cout, mode, st));
     UMT_CUDA_TRY(cudaMemsetAsync(out_umma, 0, dense, st));
-    densify_kernel<<<blocks, 256, 0, st>>>(p, L.cout, split ? 1 : 0, out_umma);
+    densify_kernel<<<blocks, 256, 0, st>>>(p, L.cout, mode, out_umma);
     UMT_TRY(check_launch("densify_kernel"));
   }
   return UMT_OK;

@@ -217,7 +217,7 @@ static int encode_all(umt_model* m, int mode, const float* images, int n_img, fl
 extern "C" int umt_model_encode(umt_model* m, int mode, const float* images, int n_img,
                                 float* features, void* stream) {
   if (!m || !images || !features) return fail(UMT_ERR_INVALID, "umt_model_encode: null argument");
-  if (mode != UMT_MODE_FP32_EQUIV && mode != UMT_MODE_BF16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
+  if (mode < UMT_MODE_FP32_EQUIV || mode > UMT_MODE_FP16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_encode: no workspace bound");
   if (n_img < 0) return fail(UMT_ERR_INVALID, "umt_model_encode: n_img=%d", n_img);
   m->launches = 0;
@@ -234,7 +234,7 @@ extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* 
                                  float* out_joint_angles, float* out_wrist, float* out_scale,
                                  float* out_sigma, void* stream) {
   if (!m) return fail(UMT_ERR_INVALID, "umt_model_forward: model is null");
-  if (mode != UMT_MODE_FP32_EQUIV && mode != UMT_MODE_BF16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
+  if (mode < UMT_MODE_FP32_EQUIV || mode > UMT_MODE_FP16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
   if (head != UMT_HEAD_KNOWN_SKELETON && head != UMT_HEAD_UNKNOWN_SKELETON)
     return fail(UMT_ERR_INVALID, "bad head %d", head);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_forward: no workspace bound");

@@ -72,6 +72,8 @@ struct ConvLayer {
   uint8_t* d_weights_hi = nullptr;                // packed [slab][2][cout][8] bf16 (hi only)
   uint8_t* d_weights2 = nullptr;                  // two-CTA packing [rank][slab][hi|lo][2][cout/2][8]
   uint8_t* d_weights2_hi = nullptr;               // two-CTA packing [rank][slab][2][cout/2][8]
+  uint8_t* d_weights_h16 = nullptr;               // fp16 weights, one-CTA packing [slab][2][cout][8]
+  uint8_t* d_weights2_h16 = nullptr;              // fp16 weights, two-CTA packing
   float* d_bias = nullptr;
   ConvParams prog{};                              // program template (tensors filled per call)
 };
@@ -130,8 +132,8 @@ size_t encoder_workspace_bytes(int chunk_images);
 void encoder_bind(umt_model* m, uint8_t* base);
 void set_conv_debug_buffer(long long* p);
 int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds);
-int launch_conv(const ConvParams& p, int cout, bool split, cudaStream_t st);
-void finalize_conv_params(ConvParams& p, const ConvLayer& L, bool split);
+int launch_conv(const ConvParams& p, int cout, int mode, cudaStream_t st);
+void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode);
 size_t flat_tensor_bytes(int H, int C, int n_img);
 FlatTensor make_flat_tensor(uint8_t* base, int H, int C, int n_img);
 // tail.cu

@@ -97,7 +97,7 @@ __device__ void load_sample_tile(const FlatTensor& T, int b, int nplanes, float*
   for (int i = threadIdx.x; i < nplanes * kPix; i += blockDim.x) {
     const int pl = i / kPix, p = i % kPix;
     float v[8];
-    load_row8<true>(T, pl, flat_row6(b, p), v);
+    load_row8<0>(T, pl, flat_row6(b, p), v);
 #pragma unroll
     for (int e = 0; e < 8; ++e) tile[(pl * 8 + e) * kPix + p] = v[e];
   }
@@ -109,7 +109,7 @@ __device__ void store_sample_tile(const FlatTensor& T, int b, int nplanes, const
     float v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) v[e] = tile[(pl * 8 + e) * kPix + p];
-    store_row8<true>(T, pl, flat_row6(b, p), v);
+    store_row8<0>(T, pl, flat_row6(b, p), v);
   }
 }
 
@@ -369,7 +369,7 @@ head_kernel(FlatTensor x /* 80 ch */, int C, const float* __restrict__ w /* [n_o
     float s = 0.f;
     for (int p = 0; p < kPix; ++p) {
       float v[8];
-      load_row8<true>(x, pl, flat_row6(b, p), v);
+      load_row8<0>(x, pl, flat_row6(b, p), v);
       s += v[e];
     }
     sMean[threadIdx.x] = s * (1.0f / 36.0f);
@@ -559,8 +559,8 @@ static int run_tail_conv(umt_model* m, int idx, const FlatTensor& src, const Fla
   p.weights = L.d_weights;
   p.bias = L.d_bias;
   p.n_pos = n_samples * kPos;
-  finalize_conv_params(p, L, /*split=*/true);
-  UMT_TRY(launch_conv(p, L.cout, true, st));
+  finalize_conv_params(p, L, UMT_MODE_FP32_EQUIV);
+  UMT_TRY(launch_conv(p, L.cout, UMT_MODE_FP32_EQUIV, st));
   ++m->launches;
   return UMT_OK;
 }

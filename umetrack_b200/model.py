@@ -62,7 +62,8 @@ class RegressorOutput:
     landmark_uncertainty_sigmas: Optional[torch.Tensor] = None
 
 
-_MODES = {"fp32": native.MODE_FP32_EQUIV, "fp32_equiv": native.MODE_FP32_EQUIV, "bf16": native.MODE_BF16}
+_MODES = {"fp32": native.MODE_FP32_EQUIV, "fp32_equiv": native.MODE_FP32_EQUIV, "bf16": native.MODE_BF16,
+          "fp16": native.MODE_FP16}
 
 
 def validate_state_dict(state_dict: Dict[str, torch.Tensor]) -> None:
@@ -117,7 +118,8 @@ class UmeTrackModel:
 
     def set_mode(self, mode: str):
         """'fp32' (default; split-bf16, three tensor-core products, fp32-equivalent results) or
-        'bf16' (single product; throughput mode, ~1e-2 relative feature error)."""
+        'bf16' (single product, ~7e-3 relative feature error) or 'fp16' (single product, 11-bit
+        significands: ~1e-3 feature error, needs activations/weights inside the half range)."""
         self._mode = _MODES[mode]
         return self
 

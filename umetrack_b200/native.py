@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libumetrack_b200.so")
 
 MODE_FP32_EQUIV = 0
 MODE_BF16 = 1
+MODE_FP16 = 2
 HEAD_KNOWN = 0
 HEAD_UNKNOWN = 1
 RESAMPLE_PARAMS = 48
