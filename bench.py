@@ -256,16 +256,39 @@ def main():
     clocks = sampler.stop(t_wall0, t_wall1)
     value = world * B * K / (ms_total * 1e-3)
 
-    # ---- end to end through the public API: pinned host inputs in, keypoints out, every step ----
+    # ---- end to end through the public API: pinned host inputs in, keypoints out, every step.
+    # The host->device copy of step i+1 runs on a copy stream while step i computes (two device
+    # input slots), the way a user feeding the model from a loader would write it; every timed step
+    # still moves its own inputs (h2d_bytes_per_step) and results (d2h_bytes_per_step). ----
     out_host = torch.empty((B, 21, 3), dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream(device=dev)
+    slots = [{k: torch.empty_like(v, device=dev) for k, v in pinned.items()} for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    state = {"i": 0}
+
+    def stage_inputs(slot):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])         # previous user of this slot is done
+            for k, v in pinned.items():
+                slots[slot][k].copy_(v, non_blocking=True)
+            ready[slot].record(copy_stream)
 
     def e2e_step():
-        dd = {k: v.to(dev, non_blocking=True) for k, v in pinned.items()}
+        slot = state["i"] & 1
+        state["i"] += 1
+        stage_inputs(slot ^ 1)                             # prefetch the next step's inputs
+        torch.cuda.current_stream().wait_event(ready[slot])
+        dd = slots[slot]
         kp = device_step(InputFrameData(dd["left_images"], dd["intrinsics"], dd["extrinsics_xf"]),
                          InputFrameDesc(dd["sample_range"], dd["memory_idx"], dd["use_memory"], dd["hand_idx"]))
+        consumed[slot].record()
         out_host.copy_(kp, non_blocking=True)
 
     pinned["use_memory"][:] = True
+    for ev in consumed:
+        ev.record()
+    stage_inputs(0)
     e2e_step()
     ms_e2e = timed(e2e_step)
     e2e_value = world * B * K / (ms_e2e * 1e-3)
