@@ -1,0 +1,64 @@
+"""Turn ncu outputs from gpurun_out/ into the small CSV summaries kept under profiles/.
+
+    python tools/summarize_ncu.py launches <ncu --csv launch list> <out.csv>
+    python tools/summarize_ncu.py full <report.ncu-rep> <out.csv> "<command line that was profiled>"
+"""
+import collections
+import csv
+import re
+import subprocess
+import sys
+
+
+def launches(src, dst):
+    rows = list(csv.reader(open(src)))
+    hi = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
+    hdr, data = rows[hi], rows[hi + 1:]
+    ki, vi, ui = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Unit")
+    agg = collections.defaultdict(lambda: [0, 0.0])
+    for r in data:
+        if len(r) <= vi:
+            continue
+        name = re.sub(r"\(.*", "", r[ki])[:80]
+        v = float(r[vi].replace(",", ""))
+        v = v / 1000 if r[ui] == "ns" else v * 1000 if r[ui] == "ms" else v
+        agg[name][0] += 1
+        agg[name][1] += v
+    tot = sum(v for _, v in agg.values())
+    with open(dst, "w") as f:
+        f.write("kernel,launches,total_us,avg_us,share\n")
+        for k, (n, v) in sorted(agg.items(), key=lambda x: -x[1][1]):
+            f.write(f"{k},{n},{v:.1f},{v / n:.1f},{v / tot:.3f}\n")
+    print(open(dst).read())
+
+
+WANT = ["Kernel Name", "launch__grid_size", "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic",
+        "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__ops_path_tensor_op_utchmma_src_fp16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
+        "sm__ops_path_tensor_op_utchmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "sm__cycles_elapsed.max"]
+
+
+def full(rep, dst, cmd):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    idx = {h: i for i, h in enumerate(hdr)}
+    cols = [w for w in WANT if w in idx]
+    with open(dst, "w") as f:
+        f.write(f"# {cmd}\n")
+        f.write(",".join(f"{w} [{units[idx[w]]}]" for w in cols) + "\n")
+        for r in data:
+            f.write(",".join('"' + r[idx[w]] + '"' for w in cols) + "\n")
+    print(open(dst).read()[:3000])
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "launches":
+        launches(sys.argv[2], sys.argv[3])
+    else:
+        full(sys.argv[2], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "")
