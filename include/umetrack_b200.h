@@ -69,6 +69,16 @@ int umt_resample_crops(const uint8_t* src_base, const int64_t* src_offset, int s
                        uint8_t* out_u8 /* [n,96,96] */, float* out_f32 /* [n,96,96] */,
                        int32_t* out_idx /* [n,96,96,4] */, void* stream);
 
+/* torch_data variant of stage (a): pinhole -> pinhole homography resampling of float32 images.
+ * Replaces `_resample_images_batched` (lib/batched_dataset/data_transform.py:78-144) and, with
+ * divide_by_255 != 0, the `/ 255` of `_perspective_crop_images` (:279).  src [n,src_h,src_w]
+ * float32; xfs [n,4,4] float32 = K_orig * E_orig * E_new^-1 * K_new^-1 (`_compute_resample_matrix`,
+ * :57-75) taking (u, v, 1) of the new image to the original; coordinates are evaluated in float64
+ * like numpy's float32 x int32 promotion; pixels whose source falls outside 0 <= x < w-1,
+ * 0 <= y < h-1 are 0.  out [n,out_h,out_w], out_w a multiple of 4. */
+int umt_resample_homography(const float* src, int src_w, int src_h, const float* xfs, int n,
+                            int out_w, int out_h, int divide_by_255, float* out, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Stage (b): per-view encoder, multi-view fusion, temporal memory, pose regression.
  * Replaces UmeTrackModel.regress_pose_use_skeleton / regress_pose_pred_skel_scale

@@ -460,3 +460,53 @@ def accel_per_frame(pts: np.ndarray, valid: np.ndarray) -> np.ndarray:
     a = np.linalg.norm(acc, axis=-1).mean(axis=-1)
     ok = valid[:, 0:-2] & valid[:, 1:-1] & valid[:, 2:]
     return a[ok]
+
+
+# ----------------------------------------------------------------------------------------
+# Stage (a), torch_data variant: pinhole -> pinhole homography resampling
+# ----------------------------------------------------------------------------------------
+
+
+def resample_matrix(k_orig: np.ndarray, orig_cam_to_world: np.ndarray, k_new: np.ndarray,
+                    new_cam_to_world: np.ndarray) -> np.ndarray:
+    """lib/batched_dataset/data_transform.py:57-75: K_orig * E_orig * E_new^-1 * K_new^-1 as
+    float32 4x4, taking a pixel (u, v, 1) of the new image to a pixel of the original."""
+    k_inv_new = np.eye(4)
+    k_inv_new[:3, :3] = np.linalg.inv(k_new)
+    k_o = np.eye(4)
+    k_o[:3, :3] = k_orig
+    m = k_o @ np.linalg.inv(orig_cam_to_world) @ new_cam_to_world @ k_inv_new
+    return m.astype(np.float32)
+
+
+def resample_homography(images_orig: np.ndarray, resample_xfs: np.ndarray, out_h: int = CROP,
+                        out_w: int = CROP) -> np.ndarray:
+    """lib/batched_dataset/data_transform.py:78-144 (`_resample_images_batched`): float32 images
+    [n,h,w], float32 transforms [n,4,4] -> float32 [n,out_h,out_w]; float64 coordinates
+    (float32 x int32 promotes), pixels outside 0 <= x < w-1, 0 <= y < h-1 stay 0, truncation to
+    the tap origin, float64 bilinear blend stored as float32."""
+    n, h, w = images_orig.shape
+    r = resample_xfs[:, 0:3, 0:3].astype(np.float64)
+    t = resample_xfs[:, 0:3, 3].astype(np.float64)
+    v, u = np.mgrid[0:out_h, 0:out_w]
+    grid = np.stack([u, v, np.ones_like(u)], axis=-1).astype(np.float64)      # [H,W,3]
+    xyz = np.einsum("nij,hwj->nhwi", r, grid) + t[:, None, None, :]
+    x = xyz[..., 0] / xyz[..., 2]
+    y = xyz[..., 1] / xyz[..., 2]
+    with np.errstate(invalid="ignore"):
+        ok = (x >= 0) & (x < w - 1) & (y >= 0) & (y < h - 1)
+    out = np.zeros((n, out_h, out_w), dtype=np.float32)
+    idx = np.nonzero(ok)
+    xs, ys = x[ok], y[ok]
+    x0 = xs.astype(np.int32)
+    y0 = ys.astype(np.int32)
+    x1, y1 = x0 + 1, y0 + 1
+    img = idx[0]
+    f00 = images_orig[img, y0, x0]
+    f01 = images_orig[img, y1, x0]
+    f10 = images_orig[img, y0, x1]
+    f11 = images_orig[img, y1, x1]
+    val = (f00 * (x1 - xs) * (y1 - ys) + f10 * (xs - x0) * (y1 - ys) + f01 * (x1 - xs) * (ys - y0)
+           + f11 * (xs - x0) * (ys - y0)) / ((x1 - x0) * (y1 - y0))
+    out[idx] = val
+    return out

@@ -196,6 +196,42 @@ def main():
         for h in range(2):
             scales.append(res.predicted_scales.get(h, np.nan))
     np.savez_compressed(os.path.join(HERE, "calibration_golden.npz"), scales=np.array(scales, dtype=np.float64))
+    # ---------------- torch_data variant: homography resampling (data_transform.py:57-144,216-281) ----
+    from lib.batched_dataset import data_transform as dt
+
+    g = np.random.default_rng(21)
+    n_frames, n_views, hh, ww = 3, 2, 96, 128
+    orig = (g.random((n_frames, n_views, hh, ww)) * 255).astype(np.float32)
+    intr = np.zeros((n_frames, n_views, 3, 3), dtype=np.float32)
+    extr = np.zeros((n_frames, n_views, 4, 4), dtype=np.float32)
+    pts = np.zeros((n_frames, 21, 3), dtype=np.float32)
+    for f in range(n_frames):
+        centre = np.array([g.uniform(-40, 40), g.uniform(-30, 30), g.uniform(280, 400)])
+        pts[f] = centre + g.normal(0, 35, size=(21, 3))
+        for v in range(n_views):
+            intr[f, v] = [[150 + 10 * v, 0, (ww - 1) / 2], [0, 150 + 10 * v, (hh - 1) / 2], [0, 0, 1]]
+            c2w = np.eye(4)
+            c2w[:3, :3] = synthetic._rot_y(0.1 * (1 - 2 * v)) @ synthetic._rot_x(0.05 * f)
+            c2w[:3, 3] = [40.0 * (2 * v - 1), 3.0 * f, 0.0]
+            extr[f, v] = np.linalg.inv(c2w)
+    td = {}
+    for hand in (0, 1):
+        imgs, ex, kk = dt._perspective_crop_images(orig, extr, intr, pts, hand, (96, 96))
+        td[f"crops_{hand}"] = imgs.astype(np.float32)
+        td[f"extr_{hand}"] = ex
+        td[f"intr_{hand}"] = kk
+    # raw kernel check: transforms that throw part of the grid outside the source image
+    xfs = np.tile(np.eye(4, dtype=np.float32), (4, 1, 1))
+    xfs[0, 0, 3] = -7.25
+    xfs[1, :2, :2] = [[1.3, 0.2], [-0.1, 0.9]]
+    xfs[1, :2, 3] = [10.5, -3.0]
+    xfs[2, 2, :] = [1e-3, -2e-3, 1.0, 0.0]          # perspective row (z depends on u, v)
+    xfs[3, :2, 3] = [200.0, 200.0]                   # everything outside -> zeros
+    src4 = (g.random((4, hh, ww)) * 255).astype(np.float32)
+    out4 = np.zeros((4, 96, 96), dtype=np.float32)
+    dt._resample_images_batched(src4, out4, xfs)
+    td["raw_xfs"], td["raw_out"] = xfs, out4
+    np.savez_compressed(os.path.join(HERE, "torchdata_golden.npz"), **td)
     print("golden written:", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))
     print("tracker per-frame error (mm):", err[:4], "n crops", len(crop_rows))
 

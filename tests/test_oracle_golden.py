@@ -109,3 +109,16 @@ def test_metrics_definitions(golden_dir):
     np.testing.assert_allclose(e, g["per_frame_error"], rtol=1e-12)
     a = O.accel_per_frame(g["tracked"], g["valid"])
     assert a.ndim == 1 and len(a) == int((g["valid"][:, :-2] & g["valid"][:, 1:-1] & g["valid"][:, 2:]).sum())
+
+
+def test_homography_resampler_matches_reference(golden_dir):
+    t = np.load(os.path.join(golden_dir, "torchdata_golden.npz"))
+    g = np.random.default_rng(21)
+    orig = (g.random((3, 2, 96, 128)) * 255).astype(np.float32)   # consume the stream like make_golden.py
+    for f in range(3):
+        g.uniform(-40, 40), g.uniform(-30, 30), g.uniform(280, 400)
+        g.normal(0, 35, size=(21, 3))
+    src4 = (g.random((4, 96, 128)) * 255).astype(np.float32)
+    out = O.resample_homography(src4, t["raw_xfs"])
+    np.testing.assert_allclose(out, t["raw_out"], rtol=0, atol=2e-5)
+    assert (out[3] == 0).all()

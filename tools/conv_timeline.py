@@ -22,7 +22,7 @@ model.set_mode(mode)
 imgs = torch.rand((n, 96, 96), device="cuda")
 model.encode(imgs)
 names = ["A:wait_empty", "A:total", "B:wait_empty", "M:wait_acc", "M:wait_a", "M:wait_b", "M:total", "M:tiles",
-         "E:wait_full", "E:total"]
+         "E:wait_full", "E:total", "g0", "g1", "sm", "M:wait_a_peer", "M:wait_b_peer"]
 for layer in layers:
     stage = 0 if layer < 4 else 1 if layer < 10 else 2 if layer < 20 else 3
     c, h = {0: (32, 48), 1: (64, 24), 2: (128, 12), 3: (256, 6)}[stage]
@@ -50,4 +50,4 @@ for layer in layers:
           f"mean CTA life {((g1 - g0).mean()) / 1e3:.1f} us, SMs used {len(per_sm)}, SMs with 2 overlapping CTAs {overlap}, "
           f"clk/us {(m[6] / ((g1 - g0).mean() / 1e3)):.0f}")
     print(f"layer {layer} ({mode}) C={out[0]} HW={out[1]} ctas={int(used.sum())} tiles/cta={m[7]:.1f}: " +
-          " ".join(f"{nm}={m[i]:.0f}" for i, nm in enumerate(names) if i != 7), flush=True)
+          " ".join(f"{nm}={m[i]:.0f}" for i, nm in enumerate(names) if i not in (7, 10, 11, 12)), flush=True)

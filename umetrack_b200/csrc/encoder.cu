@@ -647,16 +647,22 @@ conv_umma2_kernel(const __grid_constant__ ConvParams P) {
     const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
     const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)((((COUT / 2) * 16u) >> 4) & 0x3FFF) << 16);
     int it = 0, kb = 0, tc = 0;
+    long long w_acc = 0, w_a = 0, w_b = 0, w_ap = 0, w_bp = 0, t_begin = clock64(), c0 = 0;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
       const int buf = tc % n_buf;
+      c0 = P.dbg ? clock64() : 0;
       mbar_wait_cluster(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // both epilogues drained this buffer
+      if (P.dbg) w_acc += clock64() - c0;
       tc_fence_after();
       const uint32_t d_base = tmem_base + (uint32_t)buf * buf_cols;
       uint32_t any = 0;
       for (int i = 0; i < P.n_stages; ++i, ++it) {
         const int aslot = it % n_a;
+        c0 = P.dbg ? clock64() : 0;
         mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
+        if (P.dbg) { w_a += clock64() - c0; c0 = clock64(); }
         mbar_wait_cluster(a_peer(aslot), (uint32_t)(it / n_a) & 1u);
+        if (P.dbg) w_ap += clock64() - c0;
         const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
         const bool skip_hilo = SPLIT && (P.st_flags[i] & 1);   // identity (residual) slabs have w_lo == 0
         const int nt = P.st_ntaps[i];
@@ -667,8 +673,11 @@ conv_umma2_kernel(const __grid_constant__ ConvParams P) {
         for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
           const int n = min(G, nt - t0);
           const int bslot = kb % n_b;
+          c0 = P.dbg ? clock64() : 0;
           mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          if (P.dbg) { w_b += clock64() - c0; c0 = clock64(); }
           mbar_wait_cluster(b_peer(bslot), (uint32_t)(kb / n_b) & 1u);
+          if (P.dbg) w_bp += clock64() - c0;
           tc_fence_after();
           const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
           const uint32_t b_lo32 = (uint32_t)(b_desc_base & 0xFFFFFFFFu) | ((b_s0 >> 4) & 0x3FFFu);
@@ -689,6 +698,10 @@ conv_umma2_kernel(const __grid_constant__ ConvParams P) {
       }
       if (leader) tc_commit2_multicast(acc_full(buf), cta_mask);
       __syncwarp();
+    }
+    if (P.dbg && leader) {
+      long long* d = P.dbg + blockIdx.x * 16;
+      d[3] = w_acc; d[4] = w_a; d[5] = w_b; d[6] = clock64() - t_begin; d[7] = tc; d[13] = w_ap; d[14] = w_bp;
     }
   } else if (warp >= 4) {
     // ===== epilogue: TMEM -> registers -> bias / ReLU -> split bf16 -> global =====

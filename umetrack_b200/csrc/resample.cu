@@ -196,6 +196,49 @@ resample_kernel(const uint8_t* __restrict__ src_base, const int64_t* __restrict_
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// torch_data variant (lib/batched_dataset/data_transform.py:78-144): pinhole -> pinhole
+// homography resampling of float32 images.  One thread per destination pixel, float4 stores over
+// four adjacent pixels.  Coordinates are float64 like numpy's float32 x int32 promotion.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+homography_kernel(const float* __restrict__ src, int src_w, int src_h, const float* __restrict__ xfs,
+                  int n, int out_w, int out_h, int divide, float* __restrict__ out) {
+  const int groups_per_row = out_w >> 2;
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)n * out_h * groups_per_row;
+  if (gid >= total) return;
+  const int gx = (int)(gid % groups_per_row);
+  const int v = (int)((gid / groups_per_row) % out_h);
+  const int img = (int)(gid / ((long long)groups_per_row * out_h));
+  const float* M = xfs + (size_t)img * 16;
+  const float* im = src + (size_t)img * src_w * src_h;
+  float res[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const double u = (double)(gx * 4 + k), vv = (double)v;
+    // r[i,0]*u + r[i,1]*v + r[i,2]*1, then + t[i]
+    const double X = add(add(add(mul((double)M[0], u), mul((double)M[1], vv)), (double)M[2]), (double)M[3]);
+    const double Y = add(add(add(mul((double)M[4], u), mul((double)M[5], vv)), (double)M[6]), (double)M[7]);
+    const double Z = add(add(add(mul((double)M[8], u), mul((double)M[9], vv)), (double)M[10]), (double)M[11]);
+    const double x = __ddiv_rn(X, Z), y = __ddiv_rn(Y, Z);
+    float r = 0.f;
+    if (x >= 0.0 && x < (double)(src_w - 1) && y >= 0.0 && y < (double)(src_h - 1)) {
+      const int x0 = (int)x, y0 = (int)y;   // truncation, like astype(int32)
+      const double dx1 = (double)(x0 + 1) - x, dx0 = x - (double)x0;
+      const double dy1 = (double)(y0 + 1) - y, dy0 = y - (double)y0;
+      const double f00 = (double)__ldg(im + (size_t)y0 * src_w + x0), f10 = (double)__ldg(im + (size_t)y0 * src_w + x0 + 1);
+      const double f01 = (double)__ldg(im + (size_t)(y0 + 1) * src_w + x0), f11 = (double)__ldg(im + (size_t)(y0 + 1) * src_w + x0 + 1);
+      // fx_00*(x1-x)*(y1-y) + fx_10*(x-x0)*(y1-y) + fx_01*(x1-x)*(y-y0) + fx_11*(x-x0)*(y-y0)
+      const double s = add(add(add(mul(mul(f00, dx1), dy1), mul(mul(f10, dx0), dy1)), mul(mul(f01, dx1), dy0)),
+                           mul(mul(f11, dx0), dy0));
+      r = __double2float_rn(s);
+    }
+    res[k] = divide ? __fdiv_rn(r, 255.0f) : r;
+  }
+  *reinterpret_cast<float4*>(out + ((size_t)img * out_h + v) * out_w + gx * 4) = make_float4(res[0], res[1], res[2], res[3]);
+}
+
 }  // namespace
 
 extern "C" int umt_resample_crops(const uint8_t* src_base, const int64_t* src_offset,
@@ -217,4 +260,17 @@ extern "C" int umt_resample_crops(const uint8_t* src_base, const int64_t* src_of
   resample_kernel<<<n_crops * 9, kThreads, kStageBytes, (cudaStream_t)stream>>>(
       src_base, src_offset, src_pitch, src_w, src_h, params, out_u8, out_f32, out_idx);
   return umt::check_launch("resample_kernel");
+}
+
+extern "C" int umt_resample_homography(const float* src, int src_w, int src_h, const float* xfs, int n,
+                                       int out_w, int out_h, int divide_by_255, float* out, void* stream) {
+  if (n < 0 || src_w < 2 || src_h < 2 || out_w <= 0 || out_h <= 0 || (out_w & 3))
+    return umt::fail(UMT_ERR_INVALID, "umt_resample_homography: bad geometry (n=%d src %dx%d out %dx%d, out_w %% 4 must be 0)",
+                     n, src_w, src_h, out_w, out_h);
+  if (n == 0) return UMT_OK;
+  if (!src || !xfs || !out) return umt::fail(UMT_ERR_INVALID, "umt_resample_homography: null pointer");
+  const long long total = (long long)n * out_h * (out_w / 4);
+  homography_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      src, src_w, src_h, xfs, n, out_w, out_h, divide_by_255, out);
+  return umt::check_launch("homography_kernel");
 }

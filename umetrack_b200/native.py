@@ -24,6 +24,8 @@ SIGNATURES = {
     "umt_abi_version": (c_int, []),
     "umt_resample_crops": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                    c_void_p, c_void_p, c_void_p, c_void_p]),
+    "umt_resample_homography": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                                        c_void_p]),
     "umt_model_num_tensors": (c_int, []),
     "umt_model_tensor_name": (c_char_p, [c_int]),
     "umt_model_tensor_numel": (c_int64, [c_int]),
