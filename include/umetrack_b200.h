@@ -69,6 +69,26 @@ int umt_resample_crops(const uint8_t* src_base, const int64_t* src_offset, int s
                        uint8_t* out_u8 /* [n,96,96] */, float* out_f32 /* [n,96,96] */,
                        int32_t* out_idx /* [n,96,96,4] */, void* stream);
 
+/* Batched crop-camera generation (float64), one (frame, hand) item per thread.  Replaces the host
+ * loop HandTracker.gen_crop_cameras (lib/tracker/tracker.py:101-139) and below it
+ * rank_hand_visibility_in_cameras / gen_crop_cameras_from_pose (lib/tracker/perspective_crop.py:54-162,
+ * with sort_camera_index=True and at most 2 views), gen_crop_parameters_from_points
+ * (lib/common/crop.py:15-82) and make_look_at_matrix (lib/common/affine.py:34-66).
+ * crop_points [n,n_points,3] float32: FK landmarks of the given, neutral and open pose (the first 21
+ * are tested for visibility); frame_idx [n] selects the frame's cameras in cam_to_world
+ * [n_frames,n_cam,16] (mm); cam_intr [n_cam,12] = fx fy cx cy k1 k2 k3 k4 p1 p2 k5 k6; valid [n] may
+ * be NULL.  Outputs per item: sel_count [n] (0..2 cameras chosen), sel_cam [n,2], and per chosen
+ * camera the parameter row of umt_resample_crops (resample_params [n,2,48]) and the model's
+ * float32 intrinsics [n,2,3,3] / extrinsics [n,2,4,4] (world -> crop eye, metres).  *error_flag is
+ * set to 1 where the reference raises ValueError("Unable to create crop camera"), 2 on a
+ * singular camera matrix. */
+int umt_crop_cameras(const float* crop_points, const int32_t* frame_idx, const uint8_t* hand_is_right,
+                     const uint8_t* valid, const double* cam_intr, const double* cam_to_world,
+                     const double* cam_angles_deg, int n_cam, int cam_w, int cam_h, int n, int n_points,
+                     int min_vis, double focal_multiplier, int32_t* sel_count, int32_t* sel_cam,
+                     double* resample_params, float* intr_out, float* extr_out, int32_t* error_flag,
+                     void* stream);
+
 /* torch_data variant of stage (a): pinhole -> pinhole homography resampling of float32 images.
  * Replaces `_resample_images_batched` (lib/batched_dataset/data_transform.py:78-144) and, with
  * divide_by_255 != 0, the `/ 255` of `_perspective_crop_images` (:279).  src [n,src_h,src_w]
@@ -132,6 +152,18 @@ int umt_model_forward(umt_model* m, int mode, int head, const float* images,
                       int n_samples, const float* skel_axes, const float* skel_rest, int n_skel,
                       float* mem_state, float* prev_extr, int n_slots, float* out_joint_angles,
                       float* out_wrist, float* out_scale, float* out_sigma, void* stream);
+
+/* Everything after the backbone: same arguments as umt_model_forward with the per-crop
+ * `features` [n_img,72,6,6] (from umt_model_encode) in place of the images.  The backbone has no
+ * temporal dependency, so a whole recording can be encoded in one batch and this entry point
+ * stepped over its frames (fusion, lib/models/feature_extractor.py:96-141; SimpleConvRNN,
+ * temporal.py:93-139; regressor and decoders, regressor.py:163-186). */
+int umt_model_tail(umt_model* m, int head, const float* features, const float* intrinsics,
+                   const float* extrinsics, const int64_t* sample_range, const int64_t* memory_idx,
+                   const uint8_t* use_memory, const int64_t* hand_idx, int n_img, int n_samples,
+                   const float* skel_axes, const float* skel_rest, int n_skel, float* mem_state,
+                   float* prev_extr, int n_slots, float* out_joint_angles, float* out_wrist,
+                   float* out_scale, float* out_sigma, void* stream);
 
 /* Backbone only: images [n_img,96,96] -> features [n_img,72,6,6]
  * (`_image_backbone`, lib/models/model_utils.py:107-138).  Uses the bound workspace. */

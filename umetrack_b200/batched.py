@@ -1,0 +1,208 @@
+"""Batched known-skeleton tracking of whole recordings on one GPU.
+
+The reference tracks a recording frame by frame (run_eval_known_skeleton.py:48-102): crop
+cameras from the ground-truth pose, two crops per hand with cv2.remap, one model call per frame.
+Only the ConvRNN memory is sequential (lib/models/temporal.py), and the crop cameras never depend
+on earlier predictions, so this driver reorders the work without changing its result:
+
+  1. crop cameras for every (frame, hand) of every recording at once  (umt_crop_cameras, float64)
+  2. all crops of all recordings in one resampling launch              (umt_resample_crops)
+  3. the backbone over all crops in large chunks                       (umt_model_encode)
+  4. a time scan over frames; each step runs fusion + temporal memory + regressor for the hands of
+     ALL recordings that are present at that frame index               (umt_model_tail)
+  5. FK of predictions and labels, MPJPE / acceleration sums           (umt_fk_landmarks, metrics)
+
+History semantics follow HandTracker (lib/tracker/tracker.py:141-150,278-285): a hand uses its
+memory iff it was tracked in the previous frame; a frame without any hand resets both.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import native
+from .cameras import FISHEYE62_FIELDS
+from .hand_model import HandModel, load_hand_model_from_dict, scaled_hand_model
+from .hand_tracker import CONFIDENCE_THRESHOLD, HandTrackerOpts, MM_TO_M, neutral_joint_angles
+from .metrics import MetricSums
+from .model import InputFrameDesc, InputSkeletonData
+from .skinning import fk_landmarks_device
+
+
+def crop_cameras_device(hand_model: HandModel, labels: dict, device: torch.device,
+                        opts: HandTrackerOpts = HandTrackerOpts(), min_num_crops: int = 1):
+    """Crop cameras for every (frame, hand) of one recording.  Returns a dict of device tensors:
+    sel_count [T,2], sel_cam [T,2,2], resample_params [T,2,2,48] f64, intrinsics [T,2,2,3,3],
+    extrinsics [T,2,2,4,4]; hands with fewer than `min_num_crops` views get sel_count 0."""
+    cams = labels["cameras"]
+    n_cam = len(cams)
+    ja = torch.tensor(np.asarray(labels["joint_angles"]), dtype=torch.float32, device=device)          # [T,2,22]
+    wr = torch.tensor(np.asarray(labels["wrist_transforms"]), dtype=torch.float32, device=device)      # [T,2,4,4]
+    conf = np.asarray(labels["hand_confidences"], dtype=np.float64)                                    # [T,2]
+    T = ja.shape[0]
+    n = T * 2
+    # three poses per item: given, neutral, open (perspective_crop.py:89-115)
+    neutral = neutral_joint_angles(hand_model).to(device=device, dtype=torch.float32)
+    poses = torch.stack([ja.reshape(n, 22), neutral.expand(n, 22), torch.zeros((n, 22), device=device)], dim=1)
+    wrists = wr.reshape(n, 1, 4, 4).expand(n, 3, 4, 4)
+    mirror = torch.tensor([0, 1], dtype=torch.uint8, device=device).repeat(T)                          # hand index
+    n_pose = opts.num_crop_points // 21
+    pts = fk_landmarks_device(hand_model, poses[:, :n_pose].reshape(-1, 22).contiguous(),
+                              wrists[:, :n_pose].reshape(-1, 4, 4).contiguous(),
+                              mirror.repeat_interleave(n_pose)).reshape(n, n_pose * 21, 3).contiguous()
+    valid = torch.from_numpy(((conf > 0) & (conf >= CONFIDENCE_THRESHOLD)).reshape(n).astype(np.uint8)).to(device)
+    frame_idx = torch.arange(T, dtype=torch.int32, device=device).repeat_interleave(2)
+    intr = torch.tensor([[c["fx"], c["fy"], c["cx"], c["cy"]] + [c[k] for k in FISHEYE62_FIELDS] for c in cams],
+                        dtype=torch.float64, device=device)
+    c2w = torch.tensor(np.asarray(labels["camera_to_world_transforms"]), dtype=torch.float64, device=device).contiguous()
+    angles = torch.tensor(labels["camera_angles"], dtype=torch.float64, device=device)
+    sel_count = torch.zeros(n, dtype=torch.int32, device=device)
+    sel_cam = torch.zeros((n, 2), dtype=torch.int32, device=device)
+    params = torch.zeros((n, 2, 48), dtype=torch.float64, device=device)
+    k_out = torch.zeros((n, 2, 3, 3), dtype=torch.float32, device=device)
+    e_out = torch.zeros((n, 2, 4, 4), dtype=torch.float32, device=device)
+    err = torch.zeros(1, dtype=torch.int32, device=device)
+    native.check(native.lib().umt_crop_cameras(
+        native.ptr(pts), native.ptr(frame_idx), native.ptr(mirror), native.ptr(valid), native.ptr(intr),
+        native.ptr(c2w), native.ptr(angles), n_cam, int(cams[0]["ImageSizeX"]), int(cams[0]["ImageSizeY"]), n,
+        n_pose * 21, opts.min_required_vis_landmarks, float(opts.hand_ratio_in_crop), native.ptr(sel_count),
+        native.ptr(sel_cam), native.ptr(params), native.ptr(k_out), native.ptr(e_out), native.ptr(err),
+        native.current_stream_ptr()), "umt_crop_cameras")
+    code = int(err.item())
+    if code == 1:
+        raise ValueError("Unable to create crop camera")
+    if code:
+        raise native.NativeError("umt_crop_cameras: singular camera matrix")
+    sel_count = torch.where(sel_count < min_num_crops, torch.zeros_like(sel_count), sel_count)
+    return {"sel_count": sel_count.reshape(T, 2), "sel_cam": sel_cam.reshape(T, 2, 2),
+            "resample_params": params.reshape(T, 2, 2, 48), "intrinsics": k_out.reshape(T, 2, 2, 3, 3),
+            "extrinsics": e_out.reshape(T, 2, 2, 4, 4)}
+
+
+def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]],
+                             sums: Optional[MetricSums] = None, opts: HandTrackerOpts = HandTrackerOpts()):
+    """Known-skeleton tracking of several recordings [(labels, frames uint8 [T,H,n_cam*W]), ...] on
+    the current CUDA device.  Returns one dict per recording with the arrays the reference pickles
+    (tracked_keypoints, gt_keypoints [2,T,21,3] float64 mm, valid_tracking [2,T]) and
+    per_frame_mean_error; metric sums are accumulated on the GPU if `sums` is given."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    model.to(dev)
+    model.reset_memory()
+    lib = native.lib()
+    R = len(recordings)
+    hand_models = [load_hand_model_from_dict(lab["hand_model"]) for lab, _ in recordings]
+    # ---- 1. crop cameras, 2. resampling ------------------------------------------------------------
+    crops_per_rec, cams_per_rec, counts = [], [], []
+    for (lab, frames), hm in zip(recordings, hand_models):
+        cc = crop_cameras_device(hm, lab, dev, opts, min_num_crops=1)
+        T, H, W4 = frames.shape
+        n_cam = len(lab["cameras"])
+        W = W4 // n_cam
+        cnt = cc["sel_count"].cpu().numpy()                      # [T,2]
+        sel = cc["sel_cam"].cpu().numpy()                        # [T,2,2]
+        item = [(t, h, k) for t in range(T) for h in range(2) for k in range(int(cnt[t, h]))]
+        if item:
+            ti = torch.tensor([i[0] for i in item], device=dev)
+            hi = torch.tensor([i[1] for i in item], device=dev)
+            ki = torch.tensor([i[2] for i in item], device=dev)
+            params = cc["resample_params"][ti, hi, ki].contiguous()
+            offs = torch.tensor([t * H * W4 + int(sel[t, h, k]) * W for t, h, k in item], dtype=torch.int64, device=dev)
+            src = torch.from_numpy(np.ascontiguousarray(frames)).to(dev)
+            crops = torch.empty((len(item), 96, 96), dtype=torch.float32, device=dev)
+            native.check(lib.umt_resample_crops(native.ptr(src), native.ptr(offs), W4, W, H, native.ptr(params),
+                                                len(item), 0, native.ptr(crops), 0, native.current_stream_ptr()),
+                         "umt_resample_crops")
+            intr = cc["intrinsics"][ti, hi, ki].contiguous()
+            extr = cc["extrinsics"][ti, hi, ki].contiguous()
+        else:
+            crops = torch.empty((0, 96, 96), device=dev)
+            intr = torch.empty((0, 3, 3), device=dev)
+            extr = torch.empty((0, 4, 4), device=dev)
+        crops_per_rec.append(crops)
+        cams_per_rec.append((intr, extr, item))
+        counts.append(cnt)
+    # ---- 3. backbone over every crop of every recording ---------------------------------------------
+    all_crops = torch.cat(crops_per_rec, dim=0)
+    feats = model.encode(all_crops) if len(all_crops) else torch.empty((0, 72, 6, 6), device=dev)
+    all_intr = torch.cat([c[0] for c in cams_per_rec], dim=0)
+    all_extr = torch.cat([c[1] for c in cams_per_rec], dim=0)
+    base = np.cumsum([0] + [len(c) for c in crops_per_rec])
+    # crop index ranges per (recording, frame, hand)
+    start = []
+    for r, (_, _, item) in enumerate(cams_per_rec):
+        T = counts[r].shape[0]
+        s = np.zeros((T, 2), dtype=np.int64)
+        k = int(base[r])
+        for t in range(T):
+            for h in range(2):
+                s[t, h] = k
+                k += int(counts[r][t, h])
+        start.append(s)
+    # ---- 4. time scan: hands of all recordings present at frame t form one batch ---------------------
+    T_max = max(c.shape[0] for c in counts)
+    skel_axes = torch.stack([hm.joint_rotation_axes.float() for hm in hand_models]).to(dev)
+    skel_rest = torch.stack([scaled_hand_model(hm, MM_TO_M).joint_rest_positions.float() for hm in hand_models]).to(dev)
+    history = np.zeros((R, 2), dtype=bool)
+    # flat output slots: (recording r, hand h, frame t) -> off[r] + h * T_r + t
+    off = np.cumsum([0] + [2 * c.shape[0] for c in counts])
+    ja_all = torch.zeros((int(off[-1]), 22), dtype=torch.float32, device=dev)
+    wr_all = torch.eye(4, device=dev).repeat(int(off[-1]), 1, 1)
+    valid = [np.zeros((2, c.shape[0]), dtype=bool) for c in counts]
+    for t in range(T_max):
+        rows = []
+        for r in range(R):
+            if t >= counts[r].shape[0]:
+                continue
+            present = [h for h in range(2) if counts[r][t, h] > 0]
+            if not present:
+                history[r, :] = False            # frame without hands: reset_history (tracker.py:147-150)
+                continue
+            for h in present:
+                rows.append((r, h, int(start[r][t, h]), int(counts[r][t, h]), bool(history[r, h])))
+            for h in range(2):
+                history[r, h] = h in present     # tracker.py:278-285
+        if not rows:
+            continue
+        desc = InputFrameDesc(
+            sample_range=torch.tensor([[s_, s_ + c] for _, _, s_, c, _ in rows], dtype=torch.int64, device=dev),
+            memory_idx=torch.tensor([r * 2 + h for r, h, _, _, _ in rows], dtype=torch.int64, device=dev),
+            use_memory=torch.tensor([u for *_, u in rows], dtype=torch.bool, device=dev),
+            hand_idx=torch.tensor([h for _, h, _, _, _ in rows], dtype=torch.int64, device=dev))
+        ridx = torch.tensor([r for r, *_ in rows], device=dev)
+        skel = InputSkeletonData(skel_axes[ridx].contiguous(), skel_rest[ridx].contiguous())
+        o = model.regress_pose_from_features(feats, all_intr, all_extr, desc, skel)
+        slot = torch.tensor([int(off[r]) + h * counts[r].shape[0] + t for r, h, _, _, _ in rows], device=dev)
+        ja_all[slot] = o.joint_angles
+        wr_mm = o.wrist_xfs.clone()
+        wr_mm[:, :3, 3] *= 1000.0                # m -> mm (tracker.py:258)
+        wr_all[slot] = wr_mm
+        for r, h, _, _, _ in rows:
+            valid[r][h, t] = True
+    out_ja = [ja_all[int(off[r]):int(off[r + 1])] for r in range(R)]
+    out_wr = [wr_all[int(off[r]):int(off[r + 1])] for r in range(R)]
+    # ---- 5. FK + metrics -----------------------------------------------------------------------------
+    results = []
+    for r, ((lab, _), hm) in enumerate(zip(recordings, hand_models)):
+        T = counts[r].shape[0]
+        mirror = torch.tensor([0] * T + [1] * T, dtype=torch.uint8, device=dev)
+        pred = fk_landmarks_device(hm, out_ja[r].reshape(-1, 22), out_wr[r].reshape(-1, 4, 4), mirror)
+        gja = torch.tensor(np.asarray(lab["joint_angles"]), dtype=torch.float32, device=dev).permute(1, 0, 2)
+        gwr = torch.tensor(np.asarray(lab["wrist_transforms"]), dtype=torch.float32, device=dev).permute(1, 0, 2, 3)
+        gt = fk_landmarks_device(hm, gja.reshape(-1, 22).contiguous(), gwr.reshape(-1, 4, 4).contiguous(), mirror)
+        v = torch.from_numpy(valid[r].reshape(-1)).to(dev)
+        if sums is not None:
+            sums.add_errors(pred, gt, v)
+            sums.add_accelerations(pred.reshape(2, T, 21, 3), v.reshape(2, T), gt=False)
+            sums.add_accelerations(gt.reshape(2, T, 21, 3), v.reshape(2, T), gt=True)
+        tk = np.zeros((2, T, 21, 3))
+        gk = np.zeros((2, T, 21, 3))
+        pm, gm = pred.reshape(2, T, 21, 3).cpu().numpy(), gt.reshape(2, T, 21, 3).cpu().numpy()
+        tk[valid[r]] = pm[valid[r]]
+        gk[valid[r]] = gm[valid[r]]
+        err = np.linalg.norm((gk - tk)[valid[r]], axis=-1).mean(axis=-1)
+        results.append({"tracked_keypoints": tk, "gt_keypoints": gk, "valid_tracking": valid[r],
+                        "per_frame_mean_error": err})
+    return results

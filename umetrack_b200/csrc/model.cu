@@ -263,6 +263,36 @@ extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* 
 // later conv launch fills with per-role wait/total cycle counters; nullptr switches it off.
 extern "C" void umt_debug_set_conv_timeline(long long* device_buffer) { set_conv_debug_buffer(device_buffer); }
 
+extern "C" int umt_model_tail(umt_model* m, int head, const float* features, const float* intrinsics,
+                              const float* extrinsics, const int64_t* sample_range,
+                              const int64_t* memory_idx, const uint8_t* use_memory,
+                              const int64_t* hand_idx, int n_img, int n_samples, const float* skel_axes,
+                              const float* skel_rest, int n_skel, float* mem_state, float* prev_extr,
+                              int n_slots, float* out_joint_angles, float* out_wrist, float* out_scale,
+                              float* out_sigma, void* stream) {
+  if (!m) return fail(UMT_ERR_INVALID, "umt_model_tail: model is null");
+  if (head != UMT_HEAD_KNOWN_SKELETON && head != UMT_HEAD_UNKNOWN_SKELETON)
+    return fail(UMT_ERR_INVALID, "bad head %d", head);
+  if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_tail: no workspace bound");
+  if (n_img <= 0 || n_samples <= 0 || n_samples > m->ws_max_samples)
+    return fail(UMT_ERR_INVALID, "umt_model_tail: n_samples=%d exceeds the bound workspace (%d)", n_samples,
+                m->ws_max_samples);
+  if (!features || !intrinsics || !extrinsics || !sample_range || !memory_idx || !use_memory || !hand_idx ||
+      !mem_state || !prev_extr || !out_joint_angles || !out_wrist || !out_sigma)
+    return fail(UMT_ERR_INVALID, "umt_model_tail: null pointer argument");
+  if (head == UMT_HEAD_KNOWN_SKELETON) {
+    if (!skel_axes || !skel_rest || !(n_skel == 1 || n_skel == n_samples))
+      return fail(UMT_ERR_INVALID, "umt_model_tail: known-skeleton head needs 1 or n_samples skeletons");
+  } else if (!out_scale) {
+    return fail(UMT_ERR_INVALID, "umt_model_tail: unknown-skeleton head needs out_scale");
+  }
+  if (n_slots <= 0) return fail(UMT_ERR_INVALID, "umt_model_tail: n_slots=%d", n_slots);
+  m->launches = 0;
+  return tail_forward(m, head, features, intrinsics, extrinsics, sample_range, memory_idx, use_memory,
+                      hand_idx, n_img, n_samples, skel_axes, skel_rest, n_skel, mem_state, prev_extr, n_slots,
+                      out_joint_angles, out_wrist, out_scale, out_sigma, (cudaStream_t)stream);
+}
+
 extern "C" int umt_model_last_launch_count(const umt_model* m) { return m ? m->launches : 0; }
 
 extern "C" int umt_model_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,

@@ -212,11 +212,16 @@ class UmeTrackModel:
         return t.to(device=self._device, dtype=dtype).contiguous()
 
     def _forward(self, head: int, frame_data: InputFrameData, frame_desc: InputFrameDesc,
-                 skel: Optional[InputSkeletonData]) -> RegressorOutput:
+                 skel: Optional[InputSkeletonData], features: Optional[torch.Tensor] = None) -> RegressorOutput:
         self._require_handle()
-        images = self._prep(frame_data.left_images, torch.float32)
-        if images.dim() != 3 or tuple(images.shape[1:]) != (arch.CROP_SIZE, arch.CROP_SIZE):
-            raise ValueError(f"left_images must be [n,96,96], got {tuple(images.shape)}")
+        if features is not None:   # backbone already run (encode()): left_images is not used
+            images = self._prep(features, torch.float32)
+            if images.dim() != 4 or tuple(images.shape[1:]) != (arch.N_IMAGE_FEATURES, arch.FEAT_HW, arch.FEAT_HW):
+                raise ValueError(f"features must be [n,72,6,6], got {tuple(images.shape)}")
+        else:
+            images = self._prep(frame_data.left_images, torch.float32)
+            if images.dim() != 3 or tuple(images.shape[1:]) != (arch.CROP_SIZE, arch.CROP_SIZE):
+                raise ValueError(f"left_images must be [n,96,96], got {tuple(images.shape)}")
         intr = self._prep(frame_data.intrinsics, torch.float32)
         extr = self._prep(frame_data.extrinsics_xf, torch.float32)
         srange = self._prep(frame_desc.sample_range, torch.int64)
@@ -226,7 +231,7 @@ class UmeTrackModel:
         n_img, bs = images.shape[0], srange.shape[0]
         if bs == 0:
             raise ValueError("empty batch")
-        self._ensure_workspace(n_img, bs)
+        self._ensure_workspace(8 if features is not None else n_img, bs)
         # the reference reads max(memory_idx) on the host every call (temporal.py:101); do it once
         # per distinct index tensor so a steady-state loop has no host sync
         key = (mem_idx.data_ptr(), mem_idx._version, mem_idx.numel())
@@ -247,13 +252,22 @@ class UmeTrackModel:
             n_skel = axes.shape[0]
         lib = native.lib()
         with torch.cuda.device(dev):
-            native.check(lib.umt_model_forward(
-                self._handle, self._mode, head, native.ptr(images), native.ptr(intr), native.ptr(extr),
-                native.ptr(srange), native.ptr(mem_idx), native.ptr(use_mem), native.ptr(hand_idx),
-                n_img, bs, native.ptr(axes), native.ptr(rest), n_skel,
-                native.ptr(self._mem_features), native.ptr(self._prev_extrinsics),
-                len(self._mem_features), native.ptr(ja), native.ptr(wr), native.ptr(sc), native.ptr(sg),
-                native.current_stream_ptr()), "umt_model_forward")
+            if features is not None:
+                native.check(lib.umt_model_tail(
+                    self._handle, head, native.ptr(images), native.ptr(intr), native.ptr(extr),
+                    native.ptr(srange), native.ptr(mem_idx), native.ptr(use_mem), native.ptr(hand_idx),
+                    n_img, bs, native.ptr(axes), native.ptr(rest), n_skel,
+                    native.ptr(self._mem_features), native.ptr(self._prev_extrinsics),
+                    len(self._mem_features), native.ptr(ja), native.ptr(wr), native.ptr(sc), native.ptr(sg),
+                    native.current_stream_ptr()), "umt_model_tail")
+            else:
+                native.check(lib.umt_model_forward(
+                    self._handle, self._mode, head, native.ptr(images), native.ptr(intr), native.ptr(extr),
+                    native.ptr(srange), native.ptr(mem_idx), native.ptr(use_mem), native.ptr(hand_idx),
+                    n_img, bs, native.ptr(axes), native.ptr(rest), n_skel,
+                    native.ptr(self._mem_features), native.ptr(self._prev_extrinsics),
+                    len(self._mem_features), native.ptr(ja), native.ptr(wr), native.ptr(sc), native.ptr(sg),
+                    native.current_stream_ptr()), "umt_model_forward")
         self.last_launch_count = lib.umt_model_last_launch_count(self._handle)
         return RegressorOutput(joint_angles=ja, wrist_xfs=wr, skel_scales=sc, landmark_uncertainty_sigmas=sg)
 
@@ -268,6 +282,15 @@ class UmeTrackModel:
         assert bool(((r[:, 1] - r[:, 0]) != 1).all()), \
             "Unsupported: found single-view samples when calibration scale"
         return self._forward(native.HEAD_UNKNOWN, frame_data, frame_desc, None)
+
+    def regress_pose_from_features(self, features: torch.Tensor, intrinsics: torch.Tensor, extrinsics_xf: torch.Tensor,
+                                   frame_desc: InputFrameDesc, skel_data: Optional[InputSkeletonData]) -> RegressorOutput:
+        """Fusion + temporal memory + regression on backbone features computed earlier with
+        `encode()` ([n,72,6,6]); `skel_data=None` selects the unknown-skeleton head.  The backbone
+        has no temporal dependency, so recordings can be encoded as one batch and stepped here."""
+        fd = InputFrameData(features, intrinsics, extrinsics_xf)
+        head = native.HEAD_KNOWN if skel_data is not None else native.HEAD_UNKNOWN
+        return self._forward(head, fd, frame_desc, skel_data, features=features)
 
     # ---- extras ----------------------------------------------------------------------------
     def encode(self, images: torch.Tensor) -> torch.Tensor:

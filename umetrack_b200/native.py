@@ -24,6 +24,7 @@ SIGNATURES = {
     "umt_abi_version": (c_int, []),
     "umt_resample_crops": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                    c_void_p, c_void_p, c_void_p, c_void_p]),
+    "umt_crop_cameras": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_double] + [c_void_p] * 7),
     "umt_resample_homography": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                         c_void_p]),
     "umt_model_num_tensors": (c_int, []),
@@ -35,6 +36,8 @@ SIGNATURES = {
     "umt_model_bind_workspace": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
     "umt_model_forward": (c_int, [c_void_p, c_int, c_int] + [c_void_p] * 7 + [c_int, c_int, c_void_p,
                                   c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
+    "umt_model_tail": (c_int, [c_void_p, c_int] + [c_void_p] * 7 + [c_int, c_int, c_void_p,
+                               c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
     "umt_model_encode": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_encode_static": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_last_launch_count": (c_int, [c_void_p]),
