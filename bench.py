@@ -94,6 +94,81 @@ class ClockSampler:
             return None
 
 
+def measure_stages(model, hm, hm_dict, dev, peaks):
+    """Device-timed throughput of the stages around the network (north_star: achieved HBM GB/s for
+    resampling and FK), and of the batched recording pipeline that chains all of them."""
+    import numpy as np
+    import torch
+
+    from umetrack_b200 import native, synthetic
+    from umetrack_b200.batched import crop_cameras_device, track_recordings_batched
+    from umetrack_b200.skinning import fk_landmarks_device
+
+    hbm = peaks.get("hbm_gbs") or 6650.0
+    out = {"hbm_peak_gbs": hbm, "hbm_peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback"}
+
+    def timed_ms(fn, iters=10):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    # (a) fisheye -> pinhole resampling: crops of a 512-frame synthetic rig (frames exceed L2)
+    T = 512
+    labels, _ = synthetic.make_recording(hm_dict, seed=11, n_frames=T, dropouts=False, with_frames=False)
+    cc = crop_cameras_device(hm, labels, dev)
+    cnt = cc["sel_count"].cpu().numpy()
+    sel = cc["sel_cam"].cpu().numpy()
+    H, W = 480, 640
+    item = [(t, h, k) for t in range(T) for h in range(2) for k in range(int(cnt[t, h]))]
+    ti, hi, ki = (torch.tensor([i[j] for i in item], device=dev) for j in range(3))
+    params = cc["resample_params"][ti, hi, ki].contiguous()
+    offs = torch.tensor([t * H * 4 * W + int(sel[t, h, k]) * W for t, h, k in item], dtype=torch.int64, device=dev)
+    frames = torch.randint(0, 256, (T, H, 4 * W), dtype=torch.uint8, device=dev)
+    crops = torch.empty((len(item), 96, 96), dtype=torch.float32, device=dev)
+    lib = native.lib()
+
+    def run_resample():
+        native.check(lib.umt_resample_crops(frames.data_ptr(), offs.data_ptr(), 4 * W, W, H, params.data_ptr(),
+                                            len(item), 0, crops.data_ptr(), 0, native.current_stream_ptr()), "resample")
+
+    ms = timed_ms(run_resample)
+    p = params.cpu().numpy()
+    footprint = (96.0 * p[:, 0] / p[:, 28]) ** 2            # source pixels under one crop ~ (96 f_src / f_crop)^2 bytes
+    alg_bytes = float((96 * 96 * 4 + footprint).sum())
+    out["resample"] = {"crops": len(item), "ms": ms, "crops_per_s": len(item) / (ms * 1e-3),
+                       "algorithmic_bytes_per_crop": alg_bytes / len(item), "achieved_gbs": alg_bytes / (ms * 1e-3) / 1e9,
+                       "frac_of_hbm_peak": alg_bytes / (ms * 1e-3) / 1e9 / hbm,
+                       "note": "float64 camera chain per pixel: fp64-issue bound, not HBM bound"}
+    # (c) forward kinematics
+    n = 1 << 20
+    g = torch.Generator(device="cpu").manual_seed(3)
+    ja = torch.rand((n, 22), generator=g).to(dev)
+    wr = torch.eye(4).repeat(n, 1, 1).to(dev)
+    ms = timed_ms(lambda: fk_landmarks_device(hm, ja, wr))
+    fk_bytes = n * (22 * 4 + 16 * 4 + 63 * 4)
+    out["fk"] = {"poses": n, "ms": ms, "poses_per_s": n / (ms * 1e-3), "achieved_gbs": fk_bytes / (ms * 1e-3) / 1e9,
+                 "frac_of_hbm_peak": fk_bytes / (ms * 1e-3) / 1e9 / hbm}
+    # whole pipeline on recordings (BASELINE configs[1]/[4] shape): raw frames -> keypoints -> MPJPE
+    recs = [synthetic.make_recording(hm_dict, seed=100 + r, n_frames=48) for r in range(8)]
+    track_recordings_batched(model, recs[:2])
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    res = track_recordings_batched(model, recs)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    n_hf = int(sum(r["valid_tracking"].sum() for r in res))
+    out["recordings_pipeline"] = {"recordings": len(recs), "frames_each": 48, "hand_frames": n_hf, "wall_s": dt,
+                                  "hand_frames_per_s": n_hf / dt,
+                                  "note": "crop cameras + resample + encode + per-frame time scan + FK, host loop included"}
+    return out
+
+
 def cpu_oracle_rate(steps, warmup, batch=CPU_SAMPLE_BATCH):
     """hand-frames/s of the CPU restatement of the reference path (oracle port: torch fp32 model +
     FK) using every host core.  This is the one place bench.py executes oracle/."""
@@ -371,6 +446,7 @@ def main():
         model._mem_features.copy_(mem_a)
         kp_m = device_step(fd, desc)
         line["keypoint_delta_vs_fp32_mm_max"] = float((kp_ref - kp_m).abs().max())
+        line["stages"] = measure_stages(model, hm, hm_dict, dev, peaks)
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, _ = cpu_oracle_rate(steps=2, warmup=1)
             line["cpu_baseline"] = {

@@ -151,7 +151,7 @@ def load_hand_model_json(path: str) -> dict:
 
 def make_recording(hand_model_dict: dict, seed: int = 0, n_frames: int = 32,
                    width: int = 640, height: int = 480, smooth_images: bool = False,
-                   dropouts: bool = True):
+                   dropouts: bool = True, with_frames: bool = True):
     """Synthetic recording: (labels_dict in the reference JSON schema, frames uint8
     [T, H, 4*W]).  Both hands move on smooth trajectories 250-450 mm in front of the rig;
     joint angles stay inside `joint_limits`; a few confidence dropouts exercise the tracker's
@@ -188,8 +188,8 @@ def make_recording(hand_model_dict: dict, seed: int = 0, n_frames: int = 32,
     if dropouts and T >= 12:
         conf[T // 3, 0] = 0.0
         conf[T // 2: T // 2 + 2, 1] = 0.0
-    frames = g.integers(0, 256, size=(T, height, 4 * width), dtype=np.uint8)
-    if smooth_images:
+    frames = g.integers(0, 256, size=(T, height, 4 * width), dtype=np.uint8) if with_frames else None
+    if smooth_images and frames is not None:
         f = frames.astype(np.float32)
         for _ in range(2):
             f = (f + np.roll(f, 1, 1) + np.roll(f, -1, 1) + np.roll(f, 1, 2) + np.roll(f, -1, 2)) / 5
