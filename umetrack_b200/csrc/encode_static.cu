@@ -90,6 +90,7 @@ extern "C" int umt_model_encode_static(umt_model* m, int mode, const float* imag
   umt_model view;
   view.convs = m->convs;      // layer programs + device weight pointers (host-side copy only)
   view.tw = m->tw;
+  view.proj_conv = m->proj_conv;
   view.chunk_images = kStaticMaxCrops;
   view.ws = scratch;
   view.ws_bytes = kStaticScratchBytes;

@@ -190,6 +190,7 @@ struct OutPos {
   bool valid;
   int tensor;
   long long row;
+  long long dense;   // img * H * W + y * W + x (dense NCHW pixel index), for the float32 output mode
 };
 __device__ __forceinline__ OutPos map_output(long long q, int H, int W, int n_pos, int phase_out) {
   OutPos o;
@@ -198,6 +199,7 @@ __device__ __forceinline__ OutPos map_output(long long q, int H, int W, int n_po
   const int rem = (int)(q - (long long)img * S);
   const int y = rem / Wp, x = rem - y * Wp;
   o.valid = (q < n_pos) && (x < W) && (y < H);
+  o.dense = ((long long)img * H + y) * W + x;
   if (!phase_out) {
     o.tensor = 0;
     o.row = q;
@@ -482,7 +484,18 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
 #pragma unroll
               for (int e = 0; e < 8; ++e)
                 f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
-              store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
+              if (P.dense_out) {
+                // float32 NCHW output [n, dense_c, H, W]: lanes hold consecutive pixels, so for each
+                // channel the warp writes (nearly) consecutive floats
+                const long long hw = (long long)P.H * P.W, img = o.dense / hw, pix = o.dense - img * hw;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const int c = c0 + h * 8 + e;
+                  if (c < P.dense_c) P.dense_out[(img * P.dense_c + c) * hw + pix] = f[e];
+                }
+              } else {
+                store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
+              }
             }
           }
         }
@@ -733,7 +746,18 @@ conv_umma2_kernel(const __grid_constant__ ConvParams P) {
 #pragma unroll
               for (int e = 0; e < 8; ++e)
                 f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
-              store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
+              if (P.dense_out) {
+                // float32 NCHW output [n, dense_c, H, W]: lanes hold consecutive pixels, so for each
+                // channel the warp writes (nearly) consecutive floats
+                const long long hw = (long long)P.H * P.W, img = o.dense / hw, pix = o.dense - img * hw;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const int c = c0 + h * 8 + e;
+                  if (c < P.dense_c) P.dense_out[(img * P.dense_c + c) * hw + pix] = f[e];
+                }
+              } else {
+                store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
+              }
             }
           }
         }
@@ -819,7 +843,7 @@ int launch_conv(const ConvParams& p, int cout, int mode, cudaStream_t st) {
     case 128: return launch_conv_c<128>(p, mode, st);
     case 256: return launch_conv_c<256>(p, mode, st);
     // widths of the fusion / temporal / regressor layers (always fp32-equivalent)
-    case 80: if (mode == UMT_MODE_FP32_EQUIV) return launch_conv_t<80, UMT_MODE_FP32_EQUIV>(p, st); break;
+    case 80: return launch_conv_c<80>(p, mode, st);   // also the 256 -> 72 projection (all modes)
     case 96: if (mode == UMT_MODE_FP32_EQUIV) return launch_conv_t<96, UMT_MODE_FP32_EQUIV>(p, st); break;
     case 112: if (mode == UMT_MODE_FP32_EQUIV) return launch_conv_t<112, UMT_MODE_FP32_EQUIV>(p, st); break;
   }
@@ -1284,6 +1308,20 @@ int encoder_build(umt_model* m, const float* const* t) {
   m->tw.stem_w = upload(m, st.w);
   m->tw.stem_b = upload(m, st.b);
   Folded pj = folded_from(t, "_feature_extractor._image_backbone.1", "", 72, 256, 1, true);
+  {  // the projection also as a tensor-core layer: 1x1, 256 -> 72 (padded to 80), no ReLU, float32 output
+    Folded pp;
+    pp.cout = 80; pp.cin = 256; pp.ks = 1;
+    pp.w.assign((size_t)80 * 256, 0.f);
+    pp.b.assign(80, 0.f);
+    for (int co = 0; co < 72; ++co) {
+      for (int ci = 0; ci < 256; ++ci) pp.w[(size_t)co * 256 + ci] = pj.w[(size_t)co * 256 + ci];
+      pp.b[co] = pj.b[co];
+    }
+    ConvLayer L;
+    L.cout = 80; L.cin = 256; L.stride = 1; L.geom = 3; L.relu = 0; L.res_buf = -1;
+    UMT_TRY(build_conv(m, L, pp, nullptr));
+    m->proj_conv = L;
+  }
   std::vector<float> pjt((size_t)256 * 72);
   for (int co = 0; co < 72; ++co)
     for (int ci = 0; ci < 256; ++ci) pjt[(size_t)ci * 72 + co] = pj.w[(size_t)co * 256 + ci];
@@ -1439,7 +1477,19 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
     ++m->launches;
   }
   if (ev) cudaEventRecord(ev[1 + m->convs.size()], st);
-  if (features) {
+  if (features && !env_int("UMT_PROJ_SIMT", 0)) {
+    const ConvLayer& last = m->convs.back();
+    ConvParams p = m->proj_conv.prog;
+    p.src[0] = m->buf[3][last.out_buf];
+    p.res.base = nullptr;
+    p.bias = m->proj_conv.d_bias;
+    p.n_pos = n_img * 49;
+    p.dense_out = features;
+    p.dense_c = 72;
+    finalize_conv_params(p, m->proj_conv, mode);
+    UMT_TRY(launch_conv(p, 80, mode, st));
+    ++m->launches;
+  } else if (features) {
     const ConvLayer& last = m->convs.back();
     if (mode == UMT_MODE_FP32_EQUIV)
       proj_kernel<UMT_MODE_FP32_EQUIV><<<n_img, 432, 0, st>>>(m->buf[3][last.out_buf], n_img, m->tw.proj_w, m->tw.proj_b, features);

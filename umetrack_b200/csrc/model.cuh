@@ -37,6 +37,8 @@ struct ConvParams {
   FlatTensor res;           // unused by the tensor-core kernel (residuals enter as identity-weight K)
   const uint8_t* weights;   // packed operand slabs in program order
   long long w_rank_stride;  // two-CTA packing: bytes between the two CTA ranks' halves
+  float* dense_out;         // if set: write float32 NCHW [n, dense_c, H, W] instead of the planar layout
+  int dense_c;
   long long* dbg;           // optional [grid][16] cycle counters (tools/conv_timeline.py); nullptr in production
   int two_cta;              // 1: cta_group::2 kernel (cluster pair shares each MMA)
   const float* bias;        // [COUT]
@@ -105,6 +107,7 @@ struct Geometry {
 struct umt_model {
   int chunk_images = 0;
   std::vector<umt::ConvLayer> convs;      // 24 backbone convolutions in execution order
+  umt::ConvLayer proj_conv;               // 256 -> 72 projection as a tensor-core layer
   umt::TailWeights tw{};
   std::vector<void*> owned;               // device allocations to free
   // workspace binding
