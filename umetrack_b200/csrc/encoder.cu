@@ -1197,7 +1197,6 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
   while (S > 1 && S * L.cout * occ > 512) S >>= 1;
   p.S = S;
   p.n_buf = (2 * S * L.cout * occ <= 512) ? std::max(1, std::min(2, nbuf)) : 1;
-  p.order = 0;
   p.occ = occ;
   p.bgroup = std::max(1, std::min(9, G));
   p.cluster = std::max(1, std::min(2, clu));
@@ -1421,7 +1420,6 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, int 
     p.out[0] = m->buf[g][L.out_buf];
   }
   if (L.res_buf >= 0) p.src[2] = m->buf[g][L.res_buf];
-  p.res.base = nullptr;
   p.bias = L.d_bias;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);
   finalize_conv_params(p, L, mode);
@@ -1481,8 +1479,7 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
     const ConvLayer& last = m->convs.back();
     ConvParams p = m->proj_conv.prog;
     p.src[0] = m->buf[3][last.out_buf];
-    p.res.base = nullptr;
-    p.bias = m->proj_conv.d_bias;
+      p.bias = m->proj_conv.d_bias;
     p.n_pos = n_img * 49;
     p.dense_out = features;
     p.dense_c = 72;

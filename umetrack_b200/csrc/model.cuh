@@ -34,7 +34,6 @@ constexpr int kMaxTaps = 16;
 struct ConvParams {
   FlatTensor src[5];
   FlatTensor out[4];        // [0] for flat output; four parity-phase tensors when phase_out
-  FlatTensor res;           // unused by the tensor-core kernel (residuals enter as identity-weight K)
   const uint8_t* weights;   // packed operand slabs in program order
   long long w_rank_stride;  // two-CTA packing: bytes between the two CTA ranks' halves
   float* dense_out;         // if set: write float32 NCHW [n, dense_c, H, W] instead of the planar layout
@@ -51,7 +50,6 @@ struct ConvParams {
   int bgroup;               // weight slabs (taps) per B pipeline stage
   int n_buf;                // TMEM accumulator buffers (1 or 2)
   int cluster;              // CTAs per cluster sharing (multicasting) the weight slabs
-  int order;                // MMA issue order inside a slab: 0 sub-tile major, 1 product major
   int occ;                  // CTAs per SM the grid is sized for
   int n_tiles;              // tiles of S*128 positions, padded to a multiple of `cluster`
   int n_stages;
@@ -87,19 +85,10 @@ struct Folded {           // conv weight with BatchNorm folded in: w[co][ci][ks*
 
 struct TailWeights {
   // BatchNorm-folded float32 weights, device pointers
-  float *proj_w, *proj_b;                 // [72,256], [72]
-  float *fus_w[3], *fus_b[3];             // 144->108, 108->72, 72->72
-  float *tmp_w[3], *tmp_b[3];             // 90->90 x3
+  float *proj_w, *proj_b;                 // [256,72] (transposed), [72]: CUDA-core projection (UMT_PROJ_SIMT=1)
   float *skel_w, *skel_b;                 // [144,132] with BN(4) folded, [144]
-  float *reg_w[2][4], *reg_b[2][4];       // per head: four 3x3 convs [C,C,3,3] folded
-  float *head_w[2], *head_b[2];           // [n_out, C], [n_out]
+  float *head_w[2], *head_b[2];           // [n_out, 80] (zero columns for the channel padding), [n_out]
   float *stem_w, *stem_b;                 // [32,9] folded, [32]
-};
-
-struct Geometry {
-  int H, W, C;
-  long long rows;           // rows per plane (guards + padded positions)
-  int guard;
 };
 
 }  // namespace umt
@@ -114,7 +103,6 @@ struct umt_model {
   uint8_t* ws = nullptr;
   size_t ws_bytes = 0;
   int ws_max_images = 0, ws_max_samples = 0;
-  umt::Geometry geo[4]{};
   umt::FlatTensor buf[4][3]{};            // per geometry: ping, pong, mid
   umt::FlatTensor phase[4][4]{};          // phase[g]: input of geometry g (g=1..3), 4 parities
   float* feats = nullptr;                 // [max_images,72,36]

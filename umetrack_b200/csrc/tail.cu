@@ -555,7 +555,6 @@ static int run_tail_conv(umt_model* m, int idx, const FlatTensor& src, const Fla
   p.src[0] = src;
   if (res) p.src[2] = *res;
   p.out[0] = dst;
-  p.res.base = nullptr;
   p.weights = L.d_weights;
   p.bias = L.d_bias;
   p.n_pos = n_samples * kPos;
