@@ -130,29 +130,21 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
     all_intr = torch.cat([c[0] for c in cams_per_rec], dim=0)
     all_extr = torch.cat([c[1] for c in cams_per_rec], dim=0)
     base = np.cumsum([0] + [len(c) for c in crops_per_rec])
-    # crop index ranges per (recording, frame, hand)
+    # crop index ranges per (recording, frame, hand): crops are stored frame major, hand minor
     start = []
-    for r, (_, _, item) in enumerate(cams_per_rec):
-        T = counts[r].shape[0]
-        s = np.zeros((T, 2), dtype=np.int64)
-        k = int(base[r])
-        for t in range(T):
-            for h in range(2):
-                s[t, h] = k
-                k += int(counts[r][t, h])
-        start.append(s)
+    for r in range(R):
+        flat = counts[r].reshape(-1).astype(np.int64)
+        start.append((int(base[r]) + np.concatenate([[0], np.cumsum(flat)[:-1]])).reshape(counts[r].shape))
     # ---- 4. time scan: hands of all recordings present at frame t form one batch ---------------------
+    # All per-step descriptors are built on the host first (numpy), uploaded once, and the scan itself
+    # is one C call per frame index with offset pointers (UmeTrackModel.tail_scan).
     T_max = max(c.shape[0] for c in counts)
-    skel_axes = torch.stack([hm.joint_rotation_axes.float() for hm in hand_models]).to(dev)
-    skel_rest = torch.stack([scaled_hand_model(hm, MM_TO_M).joint_rest_positions.float() for hm in hand_models]).to(dev)
     history = np.zeros((R, 2), dtype=bool)
-    # flat output slots: (recording r, hand h, frame t) -> off[r] + h * T_r + t
-    off = np.cumsum([0] + [2 * c.shape[0] for c in counts])
-    ja_all = torch.zeros((int(off[-1]), 22), dtype=torch.float32, device=dev)
-    wr_all = torch.eye(4, device=dev).repeat(int(off[-1]), 1, 1)
+    off = np.cumsum([0] + [2 * c.shape[0] for c in counts])      # output slot of (r, h, t): off[r] + h*T_r + t
     valid = [np.zeros((2, c.shape[0]), dtype=bool) for c in counts]
+    rows_sr, rows_mem, rows_use, rows_hand, rows_rec, rows_slot, step_rows = [], [], [], [], [], [], []
     for t in range(T_max):
-        rows = []
+        first = len(rows_mem)
         for r in range(R):
             if t >= counts[r].shape[0]:
                 continue
@@ -161,26 +153,33 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
                 history[r, :] = False            # frame without hands: reset_history (tracker.py:147-150)
                 continue
             for h in present:
-                rows.append((r, h, int(start[r][t, h]), int(counts[r][t, h]), bool(history[r, h])))
+                s0 = int(start[r][t, h])
+                rows_sr.append((s0, s0 + int(counts[r][t, h])))
+                rows_mem.append(r * 2 + h)
+                rows_use.append(bool(history[r, h]))
+                rows_hand.append(h)
+                rows_rec.append(r)
+                rows_slot.append(int(off[r]) + h * counts[r].shape[0] + t)
+                valid[r][h, t] = True
             for h in range(2):
                 history[r, h] = h in present     # tracker.py:278-285
-        if not rows:
-            continue
-        desc = InputFrameDesc(
-            sample_range=torch.tensor([[s_, s_ + c] for _, _, s_, c, _ in rows], dtype=torch.int64, device=dev),
-            memory_idx=torch.tensor([r * 2 + h for r, h, _, _, _ in rows], dtype=torch.int64, device=dev),
-            use_memory=torch.tensor([u for *_, u in rows], dtype=torch.bool, device=dev),
-            hand_idx=torch.tensor([h for _, h, _, _, _ in rows], dtype=torch.int64, device=dev))
-        ridx = torch.tensor([r for r, *_ in rows], device=dev)
-        skel = InputSkeletonData(skel_axes[ridx].contiguous(), skel_rest[ridx].contiguous())
-        o = model.regress_pose_from_features(feats, all_intr, all_extr, desc, skel)
-        slot = torch.tensor([int(off[r]) + h * counts[r].shape[0] + t for r, h, _, _, _ in rows], device=dev)
-        ja_all[slot] = o.joint_angles
-        wr_mm = o.wrist_xfs.clone()
-        wr_mm[:, :3, 3] *= 1000.0                # m -> mm (tracker.py:258)
-        wr_all[slot] = wr_mm
-        for r, h, _, _, _ in rows:
-            valid[r][h, t] = True
+        step_rows.append((first, len(rows_mem) - first))
+    ja_all = torch.zeros((int(off[-1]), 22), dtype=torch.float32, device=dev)
+    wr_all = torch.eye(4, device=dev).repeat(int(off[-1]), 1, 1)
+    if rows_mem:
+        skel_axes = torch.stack([hm.joint_rotation_axes.float() for hm in hand_models]).to(dev)
+        skel_rest = torch.stack([scaled_hand_model(hm, MM_TO_M).joint_rest_positions.float() for hm in hand_models]).to(dev)
+        ridx = torch.tensor(rows_rec, device=dev)
+        ja, wr, _ = model.tail_scan(
+            feats, all_intr, all_extr, step_rows,
+            torch.tensor(rows_sr, dtype=torch.int64, device=dev), torch.tensor(rows_mem, dtype=torch.int64, device=dev),
+            torch.tensor(rows_use, dtype=torch.bool, device=dev), torch.tensor(rows_hand, dtype=torch.int64, device=dev),
+            skel_axes[ridx].contiguous(), skel_rest[ridx].contiguous(), n_slots=2 * R)
+        slot = torch.tensor(rows_slot, device=dev)
+        wr = wr.clone()
+        wr[:, :3, 3] *= 1000.0                   # m -> mm (tracker.py:258)
+        ja_all[slot] = ja
+        wr_all[slot] = wr
     out_ja = [ja_all[int(off[r]):int(off[r + 1])] for r in range(R)]
     out_wr = [wr_all[int(off[r]):int(off[r + 1])] for r in range(R)]
     # ---- 5. FK + metrics -----------------------------------------------------------------------------

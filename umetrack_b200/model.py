@@ -292,6 +292,51 @@ class UmeTrackModel:
         head = native.HEAD_KNOWN if skel_data is not None else native.HEAD_UNKNOWN
         return self._forward(head, fd, frame_desc, skel_data, features=features)
 
+    def tail_scan(self, features: torch.Tensor, intrinsics: torch.Tensor, extrinsics_xf: torch.Tensor,
+                  step_rows, sample_range: torch.Tensor, memory_idx: torch.Tensor, use_memory: torch.Tensor,
+                  hand_idx: torch.Tensor, skel_axes: torch.Tensor, skel_rest: torch.Tensor, n_slots: int):
+        """Time scan for batched recordings: `step_rows` is a list of (first_row, n_rows); the
+        descriptor tensors hold the rows of ALL steps back to back (already on the device), so a step
+        is one C call with offset pointers -- no tensor construction, no host sync.  Uses the
+        known-skeleton head with one skeleton per row.  Returns (joint_angles [rows,22], wrist_xfs
+        [rows,4,4] in metres, sigmas [rows,21]) in row order."""
+        self._require_handle()
+        dev = self._device
+        feats = self._prep(features, torch.float32)
+        intr = self._prep(intrinsics, torch.float32)
+        extr = self._prep(extrinsics_xf, torch.float32)
+        sr = self._prep(sample_range, torch.int64)
+        mi = self._prep(memory_idx, torch.int64)
+        um = self._prep(use_memory, torch.bool)
+        hi = self._prep(hand_idx, torch.int64)
+        ax = self._prep(skel_axes, torch.float32)
+        rs = self._prep(skel_rest, torch.float32)
+        rows = sr.shape[0]
+        max_rows = max((n for _, n in step_rows), default=0)
+        self._ensure_workspace(8, max(max_rows, 8))
+        self._grow_memory(n_slots)
+        ja = torch.empty((rows, 22), dtype=torch.float32, device=dev)
+        wr = torch.empty((rows, 4, 4), dtype=torch.float32, device=dev)
+        sg = torch.empty((rows, 21), dtype=torch.float32, device=dev)
+        lib = native.lib()
+        stream = native.current_stream_ptr()
+        n_img = feats.shape[0]
+        p = {k: t.data_ptr() for k, t in dict(sr=sr, mi=mi, um=um, hi=hi, ax=ax, rs=rs, ja=ja, wr=wr, sg=sg).items()}
+        launches = 0
+        with torch.cuda.device(dev):
+            for first, n in step_rows:
+                if n == 0:
+                    continue
+                native.check(lib.umt_model_tail(
+                    self._handle, native.HEAD_KNOWN, feats.data_ptr(), intr.data_ptr(), extr.data_ptr(),
+                    p["sr"] + first * 16, p["mi"] + first * 8, p["um"] + first, p["hi"] + first * 8, n_img, n,
+                    p["ax"] + first * 264, p["rs"] + first * 264, n, self._mem_features.data_ptr(),
+                    self._prev_extrinsics.data_ptr(), len(self._mem_features), p["ja"] + first * 88,
+                    p["wr"] + first * 64, 0, p["sg"] + first * 84, stream), "umt_model_tail")
+                launches += lib.umt_model_last_launch_count(self._handle)
+        self.last_launch_count = launches
+        return ja, wr, sg
+
     # ---- extras ----------------------------------------------------------------------------
     def encode(self, images: torch.Tensor) -> torch.Tensor:
         """Backbone only: [n,96,96] -> [n,72,6,6] (the reference's `_image_backbone`)."""
