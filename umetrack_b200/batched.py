@@ -85,7 +85,9 @@ def crop_cameras_device(hand_model: HandModel, labels: dict, device: torch.devic
 def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]],
                              sums: Optional[MetricSums] = None, opts: HandTrackerOpts = HandTrackerOpts()):
     """Known-skeleton tracking of several recordings [(labels, frames uint8 [T,H,n_cam*W]), ...] on
-    the current CUDA device.  Returns one dict per recording with the arrays the reference pickles
+    the current CUDA device.  `frames` is a numpy array or a torch tensor; a tensor in pinned host
+    memory is uploaded asynchronously (the upload of the raw frames is the largest single cost of
+    this driver), a tensor already on the device is used in place.  Returns one dict per recording with the arrays the reference pickles
     (tracked_keypoints, gt_keypoints [2,T,21,3] float64 mm, valid_tracking [2,T]) and
     per_frame_mean_error; metric sums are accumulated on the GPU if `sums` is given."""
     dev = torch.device("cuda", torch.cuda.current_device())
@@ -103,14 +105,18 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
         W = W4 // n_cam
         cnt = cc["sel_count"].cpu().numpy()                      # [T,2]
         sel = cc["sel_cam"].cpu().numpy()                        # [T,2,2]
-        item = [(t, h, k) for t in range(T) for h in range(2) for k in range(int(cnt[t, h]))]
-        if item:
-            ti = torch.tensor([i[0] for i in item], device=dev)
-            hi = torch.tensor([i[1] for i in item], device=dev)
-            ki = torch.tensor([i[2] for i in item], device=dev)
+        # crops are stored frame major, hand minor, view minor-most
+        t_i, h_i, k_i = np.nonzero(np.arange(sel.shape[2])[None, None, :] < cnt[:, :, None])
+        item = t_i
+        if len(item):
+            thk = torch.from_numpy(np.stack([t_i, h_i, k_i])).to(dev)
+            ti, hi, ki = thk[0], thk[1], thk[2]
             params = cc["resample_params"][ti, hi, ki].contiguous()
-            offs = torch.tensor([t * H * W4 + int(sel[t, h, k]) * W for t, h, k in item], dtype=torch.int64, device=dev)
-            src = torch.from_numpy(np.ascontiguousarray(frames)).to(dev)
+            offs = torch.from_numpy(t_i.astype(np.int64) * (H * W4) + sel[t_i, h_i, k_i].astype(np.int64) * W).to(dev)
+            if isinstance(frames, torch.Tensor):
+                src = frames.contiguous().to(dev, non_blocking=True)
+            else:
+                src = torch.from_numpy(np.ascontiguousarray(frames)).to(dev)
             crops = torch.empty((len(item), 96, 96), dtype=torch.float32, device=dev)
             native.check(lib.umt_resample_crops(native.ptr(src), native.ptr(offs), W4, W, H, native.ptr(params),
                                                 len(item), 0, native.ptr(crops), 0, native.current_stream_ptr()),
