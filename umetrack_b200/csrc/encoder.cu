@@ -260,7 +260,11 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
 // MMAs of tile i+1.  With a cluster of `cluster` CTAs the weight slabs -- identical for every
 // tile -- are fetched from L2 once per cluster: each CTA loads 1/cluster of a slab and multicasts
 // it into the shared memory of all CTAs of the cluster.
-template <int COUT, int MODE>
+// EPI selects the epilogue (kept out of the loop body at compile time: the epilogue warps run one
+// warp per scheduler, so every instruction they fetch is on the path that frees the accumulator):
+// 0 = bias/ReLU -> planar rows, 1 = + identity residual, 2 = float32 NCHW output (projection).
+constexpr int kEpiPlain = 0, kEpiResidual = 1, kEpiDense = 2;
+template <int COUT, int MODE, int EPI>
 __global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma_kernel(const __grid_constant__ ConvParams P) {
   constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
@@ -458,16 +462,33 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     long long w_full = 0, t_begin = clock64();
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
       const int buf = tc % n_buf;
+      const long long q0 = (long long)tile * mc;
+      constexpr int kStep = (COUT % 32 == 0) ? 32 : 16;   // columns per TMEM round trip
+      constexpr int kRows = kStep / 8;
+      // identity residual: the rows of the NEXT chunk are requested before the current chunk is
+      // processed (and the first chunk's before the accumulator is awaited)
+      uint4 rn_h[kRows], rn_l[kRows];
+      auto res_fetch = [&](long long q, bool valid, int c0) {
+        const uint8_t* g = P.res.base + (long long)(c0 >> 3) * P.res.plane_stride + (P.res.guard + q) * 16;
+#pragma unroll
+        for (int h = 0; h < kRows; ++h) {
+          if (valid) {
+            rn_h[h] = __ldg(reinterpret_cast<const uint4*>(g + (long long)h * P.res.plane_stride));
+            if (SPLIT) rn_l[h] = __ldg(reinterpret_cast<const uint4*>(g + (long long)h * P.res.plane_stride + P.res.lo_offset));
+          }
+        }
+      };
+      OutPos o_next = map_output(q0 + lgrp * 32 + lane, P.H, P.W, P.n_pos, P.phase_out);
+      if (EPI == kEpiResidual) res_fetch(q0 + lgrp * 32 + lane, o_next.valid, 0);
       const long long c0 = P.dbg ? clock64() : 0;
       mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
       if (P.dbg) w_full += clock64() - c0;
       tc_fence_after();
-      const long long q0 = (long long)tile * mc;
       for (int s = 0; s < P.S; ++s) {
         const long long q = q0 + s * 128 + lgrp * 32 + lane;
-        const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
+        const OutPos o = o_next;
+        if (s + 1 < P.S) o_next = map_output(q + 128, P.H, P.W, P.n_pos, P.phase_out);
         const FlatTensor& T = P.out[o.tensor];
-        constexpr int kStep = (COUT % 32 == 0) ? 32 : 16;   // columns per TMEM round trip
         const float lo_clamp = P.relu ? 0.0f : -INFINITY;
 #pragma unroll 1
         for (int c0 = 0; c0 < COUT; c0 += kStep) {
@@ -476,15 +497,29 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
                                  (uint32_t)buf * buf_cols + (uint32_t)(s * COUT + c0);
           tc_ld16(taddr, v);
           if (kStep == 32) tc_ld16(taddr + 16, v + 16);
+          uint4 rc_h[kRows], rc_l[kRows];
+          if (EPI == kEpiResidual) {
+#pragma unroll
+            for (int h = 0; h < kRows; ++h) { rc_h[h] = rn_h[h]; if (SPLIT) rc_l[h] = rn_l[h]; }
+            if (c0 + kStep < COUT) res_fetch(q, o.valid, c0 + kStep);
+            else if (s + 1 < P.S) res_fetch(q + 128, o_next.valid, 0);
+          }
           tc_ld_wait();
           if (o.valid) {
 #pragma unroll
             for (int h = 0; h < kStep / 8; ++h) {
               float f[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e)
-                f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
-              if (P.dense_out) {
+              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e];
+              if (EPI == kEpiResidual) {
+                float r[8];
+                decode_row8<MODE>(rc_h[h], rc_l[h], r);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) f[e] += r[e];
+              }
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], lo_clamp);
+              if (EPI == kEpiDense) {
                 // float32 NCHW output [n, dense_c, H, W]: lanes hold consecutive pixels, so for each
                 // channel the warp writes (nearly) consecutive floats
                 const long long hw = (long long)P.H * P.W, img = o.dense / hw, pix = o.dense - img * hw;
@@ -804,7 +839,17 @@ static int sm_count() {
 template <int COUT, int MODE>
 static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   const size_t smem = conv_smem_bytes(p, COUT, MODE == UMT_MODE_FP32_EQUIV);
-  auto kernel = p.two_cta ? conv_umma2_kernel<COUT, MODE> : conv_umma_kernel<COUT, MODE>;
+  void (*kernel)(ConvParams) = conv_umma_kernel<COUT, MODE, kEpiPlain>;
+  if (p.two_cta) {
+    if (p.res_epi) return fail(UMT_ERR_INVALID, "two-CTA conv kernel has no residual epilogue");
+    kernel = conv_umma2_kernel<COUT, MODE>;
+  } else if (p.dense_out) {
+    if constexpr (COUT == 80) kernel = conv_umma_kernel<COUT, MODE, kEpiDense>;
+    else return fail(UMT_ERR_UNSUPPORTED, "float32 output epilogue only for the projection width");
+    if (p.res_epi) return fail(UMT_ERR_INVALID, "float32 output epilogue has no residual");
+  } else if (p.res_epi) {
+    kernel = conv_umma_kernel<COUT, MODE, kEpiResidual>;
+  }
   ConvParams pd = p;
   pd.dbg = g_conv_dbg;
   UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -890,6 +935,7 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int mode,
     }
   }
   acc += P.bias[co];
+  if (P.res_epi) acc += load_elem(P.res, mode, co, q);
   if (P.relu) acc = fmaxf(acc, 0.f);
   out[(((size_t)img * cout + co) * P.H + y) * P.W + x] = acc;
 }
@@ -1127,10 +1173,13 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
       for (int ky = 0; ky < 3; ++ky)
         for (int kx = 0; kx < 3; ++kx) pack_slab(blob, main, c, ky, kx);
     }
+    // identity residual (backbone_resnet.py:66-69).  Two ways, chosen per launch in
+    // finalize_conv_params: (a) the epilogue re-reads x (prefetched one chunk ahead) and adds it in
+    // float32, or (b) x enters the accumulator as extra K through identity weight slabs (source 2,
+    // centre tap), exactly as hi + lo.  The identity stages are the LAST stages of the program so
+    // that (a) simply stops before them.
     if (L.res_buf >= 0) {
-      // identity residual (backbone_resnet.py:66-69): x enters the accumulator as extra K through
-      // identity weight slabs (source 2, centre tap), exactly as hi + lo, instead of being re-read
-      // by the epilogue
+      p.res_stages = L.cout / 16;
       for (int c = 0; c < L.cout / 16; ++c) {
         p.st_src[ns] = 2; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = 1; p.st_tap0[ns] = 4;
         p.st_flags[ns] = 1;
@@ -1138,6 +1187,7 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
         pack_identity_slab(blob, L.cout, c);
       }
     }
+    if (ds && L.res_buf >= 0) return fail(UMT_ERR_INVALID, "conv: identity residual and downsample branch together");
     if (ds) {  // fused 1x1 stride-2 downsample: source 1 = parity-phase (0,0) of the block input
       for (int c = 0; c < ds->cin / 16; ++c) {
         p.st_src[ns] = 1; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = 1; p.st_tap0[ns] = 4;
@@ -1419,7 +1469,7 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, int 
   } else {
     p.out[0] = m->buf[g][L.out_buf];
   }
-  if (L.res_buf >= 0) p.src[2] = m->buf[g][L.res_buf];
+  if (L.res_buf >= 0) { p.src[2] = m->buf[g][L.res_buf]; p.res = p.src[2]; }
   p.bias = L.d_bias;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);
   finalize_conv_params(p, L, mode);
@@ -1433,6 +1483,15 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   } else {
     p.weights = split ? L.d_weights : (mode == UMT_MODE_FP16 ? L.d_weights_h16 : L.d_weights_hi);
     p.w_rank_stride = 0;
+  }
+  // identity residual: through the epilogue or through identity slabs?  (B200, round 1: the
+  // one-MMA identity stages cost a full pipeline hand-shake each, so the epilogue wins wherever
+  // it is not itself the bottleneck -- everywhere in the 3-product mode, and for Cout >= 64 in
+  // the 16-bit modes.)  UMT_RES_MMA=0/1 forces one way.
+  if (p.res_stages > 0) {
+    const int force = env_int("UMT_RES_MMA", -1);
+    const bool epi = !p.two_cta && (force >= 0 ? force == 0 : (split || L.cout >= 64));
+    if (epi) { p.n_stages -= p.res_stages; p.res_epi = 1; }
   }
   // pipeline depths from the shared-memory budget
   const int mc = p.S * 128;

@@ -71,6 +71,22 @@ __device__ __forceinline__ void load_row8(const FlatTensor& t, int plane, long l
   }
 }
 
+// decode one already-loaded row (hi [+ lo]) into 8 floats
+template <int MODE>
+__device__ __forceinline__ void decode_row8(const uint4& h, const uint4& l, float* v) {
+  if (MODE == 2) {
+    float2 a = unpack_f16x2(h.x), b = unpack_f16x2(h.y), c = unpack_f16x2(h.z), d = unpack_f16x2(h.w);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+    return;
+  }
+  v[0] = bf16_lo(h.x); v[1] = bf16_hi(h.x); v[2] = bf16_lo(h.y); v[3] = bf16_hi(h.y);
+  v[4] = bf16_lo(h.z); v[5] = bf16_hi(h.z); v[6] = bf16_lo(h.w); v[7] = bf16_hi(h.w);
+  if (MODE == 0) {
+    v[0] += bf16_lo(l.x); v[1] += bf16_hi(l.x); v[2] += bf16_lo(l.y); v[3] += bf16_hi(l.y);
+    v[4] += bf16_lo(l.z); v[5] += bf16_hi(l.z); v[6] += bf16_lo(l.w); v[7] += bf16_hi(l.w);
+  }
+}
+
 // one element of a stored row (test hooks)
 __device__ __forceinline__ float load_elem(const FlatTensor& t, int mode, int c, long long row) {
   const uint8_t* p = t.base + (long long)(c >> 3) * t.plane_stride + (t.guard + row) * 16;

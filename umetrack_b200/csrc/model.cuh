@@ -55,6 +55,9 @@ struct ConvParams {
   int n_stages;
   int phase_out;            // 1: scatter the output into four (H/2, W/2) parity-phase tensors
   int relu;                 // 1: ReLU in the epilogue
+  int res_epi;              // 1: the epilogue adds the identity residual `res` (same raster as the output)
+  int res_stages;           // trailing program stages that feed the same residual through identity slabs
+  FlatTensor res;
   uint8_t st_src[kMaxStages], st_chunk[kMaxStages], st_ntaps[kMaxStages], st_tap0[kMaxStages];
   uint8_t st_flags[kMaxStages];   // bit 0: weight slab has no lo part (identity slab of a residual)
   short tap_shift[kMaxTaps];

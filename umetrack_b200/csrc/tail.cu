@@ -553,7 +553,7 @@ static int run_tail_conv(umt_model* m, int idx, const FlatTensor& src, const Fla
   const ConvLayer& L = m->tail_convs[idx];
   ConvParams p = L.prog;
   p.src[0] = src;
-  if (res) p.src[2] = *res;
+  if (res) { p.src[2] = *res; p.res = *res; }
   p.out[0] = dst;
   p.weights = L.d_weights;
   p.bias = L.d_bias;
