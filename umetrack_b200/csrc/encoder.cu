@@ -479,7 +479,21 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
         }
       };
       OutPos o_next = map_output(q0 + lgrp * 32 + lane, P.H, P.W, P.n_pos, P.phase_out);
-      if (EPI == kEpiResidual) res_fetch(q0 + lgrp * 32 + lane, o_next.valid, 0);
+      if (EPI == kEpiResidual) {
+        res_fetch(q0 + lgrp * 32 + lane, o_next.valid, 0);
+        // the accumulator is still being computed: pull the rest of this tile's residual rows
+        // into L2 now (they were written two layers ago and have usually been evicted)
+        if (q0 + (long long)P.S * 128 <= P.n_pos) {
+          for (int s = 0; s < P.S; ++s) {
+            const uint8_t* g = P.res.base + (P.res.guard + q0 + s * 128 + lgrp * 32 + lane) * 16;
+#pragma unroll 4
+            for (int pl = 0; pl < COUT / 8; ++pl) {
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(g + (long long)pl * P.res.plane_stride));
+              if (SPLIT) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + (long long)pl * P.res.plane_stride + P.res.lo_offset));
+            }
+          }
+        }
+      }
       const long long c0 = P.dbg ? clock64() : 0;
       mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
       if (P.dbg) w_full += clock64() - c0;
