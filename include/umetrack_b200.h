@@ -225,6 +225,19 @@ int umt_mpjpe_accumulate(const float* pred, const float* gt, const uint8_t* vali
 int umt_accel_accumulate(const float* pts, const uint8_t* valid, int n_seq, int T, double* sums,
                          void* stream);
 
+/* Per-hand-frame keypoint error err[i] = mean_21 |gt_i - pred_i|_2 in float64, evaluated in the
+ * order numpy uses for np.linalg.norm(d, axis=-1).mean(axis=-1) (run_eval_known_skeleton.py:88-89,
+ * load_eval.py:33-34: ((dx^2+dy^2)+dz^2, eight partial sums over the 21 landmarks), so the values
+ * are bit-identical to the reference's for float32-valued keypoints.  pred/gt [n,21,3] float32. */
+int umt_keypoint_errors(const float* pred, const float* gt, int n, double* err, void* stream);
+
+/* PCK counts (lib/common/metric_utils.py:36-88 as used by load_eval.py:66-72):
+ * counts[k] += number of i with valid[i] (NULL = all) and err[i] <= thresholds[k].
+ * thresholds: ascending float64 [n_thresholds <= 1024]; counts float64 [n_thresholds]
+ * (integers, exact below 2^53; float64 so that they ride in the same all-reduce as the sums). */
+int umt_pck_accumulate(const double* err, const uint8_t* valid, long long n, const double* thresholds,
+                       int n_thresholds, double* counts, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

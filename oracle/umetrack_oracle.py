@@ -510,3 +510,53 @@ def resample_homography(images_orig: np.ndarray, resample_xfs: np.ndarray, out_h
            + f11 * (xs - x0) * (ys - y0)) / ((x1 - x0) * (y1 - y0))
     out[idx] = val
     return out
+
+
+# ----------------------------------------------------------------------------------------
+# Aggregate metrics: PCK curve, normalised AUC, success rate
+# ----------------------------------------------------------------------------------------
+
+MAX_LANDMARK_ERROR_MM = 50                                   # lib/common/metric_utils.py:19
+PCK_THRESHOLDS = np.linspace(0, MAX_LANDMARK_ERROR_MM, 101)  # lib/common/metric_utils.py:20
+
+
+def pck_curve(errors: np.ndarray, thresholds: np.ndarray, mask: Optional[np.ndarray] = None,
+              axis: Optional[int] = None) -> np.ndarray:
+    """lib/common/metric_utils.py:36-88: fraction of (masked) errors <= each threshold; one curve
+    per element along `axis` if given.  Rows with an empty mask give 0 (their _safe_div)."""
+    if mask is None:
+        mask = np.ones_like(errors)
+    if axis is None:
+        e, m = errors.reshape(-1), mask.reshape(-1)
+    else:
+        n = errors.shape[axis]
+        e, m = np.moveaxis(errors, axis, 0).reshape(n, -1), np.moveaxis(mask, axis, 0).reshape(n, -1)
+    rows = []
+    for t in thresholds:
+        num, den = ((e <= t) * m).sum(axis=-1), m.sum(axis=-1)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            z = np.asarray(num / den, dtype=np.float64)
+        rows.append(np.where(den < 1e-6, 0.0, z))
+    return np.stack(rows).T
+
+
+def normalized_auc(x: np.ndarray, y: np.ndarray, y_max: float = 1.0) -> np.ndarray:
+    """lib/common/metric_utils.py:91-112: trapezoid area over (x[-1]-x[0]) * y_max."""
+    shape = y.shape[:-1]
+    y2 = y.reshape(-1, y.shape[-1])
+    auc = ((x[1:] - x[:-1]).reshape(1, -1) * ((y2[..., 1:] + y2[..., :-1]) * 0.5)).sum(axis=-1)
+    return (auc / ((x[-1] - x[0]) * y_max)).reshape(shape)
+
+
+def aggregate_metrics(records) -> dict:
+    """load_eval.py:47-89 on a list of {"tracked_keypoints","gt_keypoints","valid_tracking"} dicts:
+    the five numbers it prints plus the PCK curve (in percent, as it passes it to the AUC)."""
+    errs = np.concatenate([mpjpe_per_frame(r["gt_keypoints"], r["tracked_keypoints"], r["valid_tracking"]) for r in records])
+    acc = np.concatenate([accel_per_frame(r["tracked_keypoints"], r["valid_tracking"]) for r in records])
+    gacc = np.concatenate([accel_per_frame(r["gt_keypoints"], r["valid_tracking"]) for r in records])
+    pck = pck_curve(errs, PCK_THRESHOLDS) * 100.0
+    valid = np.concatenate([r["valid_tracking"] for r in records], axis=1)
+    return {"n_valid": int(valid.sum()), "n_total": int(valid.size),
+            "success_rate": float(valid.sum() / valid.size * 100), "mean_keypoint_error": float(errs.mean()),
+            "auc": float(normalized_auc(PCK_THRESHOLDS, pck)), "pck_curve": pck,
+            "mean_keypoint_acceleration": float(acc.mean()), "gt_mean_keypoint_acceleration": float(gacc.mean())}

@@ -36,3 +36,15 @@ def pack_resample_params(sf, sc, coeffs, sxf, cf, cc, cxf):
     return np.concatenate([np.asarray(sf, float), np.asarray(sc, float), np.asarray(coeffs, float),
                            np.asarray(sxf, float).reshape(-1), np.asarray(cf, float), np.asarray(cc, float),
                            np.asarray(cxf, float).reshape(-1)])
+
+
+def aggregate_inputs():
+    """The seeded eval results the aggregate goldens were generated from
+    (tests/golden/make_aggregate_golden.py:aggregate_inputs)."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("make_aggregate_golden",
+                                                  os.path.join(GOLDEN, "make_aggregate_golden.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.aggregate_inputs()

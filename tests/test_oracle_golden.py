@@ -122,3 +122,33 @@ def test_homography_resampler_matches_reference(golden_dir):
     out = O.resample_homography(src4, t["raw_xfs"])
     np.testing.assert_allclose(out, t["raw_out"], rtol=0, atol=2e-5)
     assert (out[3] == 0).all()
+
+
+def test_aggregate_metrics_oracle_matches_reference(golden_dir):
+    """PCK curve, AUC and the load_eval summary against the reference's outputs."""
+    from tests.helpers import aggregate_inputs
+
+    g = np.load(os.path.join(golden_dir, "aggregate_golden.npz"))
+    recs = aggregate_inputs()
+    errs = []
+    for i, r in enumerate(recs):
+        e = O.mpjpe_per_frame(r["gt_keypoints"], r["tracked_keypoints"], r["valid_tracking"])
+        assert np.array_equal(e, g[f"errors_{i}"])
+        assert np.array_equal(O.accel_per_frame(r["tracked_keypoints"], r["valid_tracking"]), g[f"accel_{i}"])
+        assert np.array_equal(O.accel_per_frame(r["gt_keypoints"], r["valid_tracking"]), g[f"gt_accel_{i}"])
+        errs.append(e)
+    errs = np.concatenate(errs)
+    assert np.array_equal(O.PCK_THRESHOLDS, g["thresholds"])
+    pck = O.pck_curve(errs, O.PCK_THRESHOLDS) * 100.0
+    assert np.array_equal(pck, g["pck_curve"])
+    assert float(O.normalized_auc(O.PCK_THRESHOLDS, pck)) == float(g["auc"])
+    e2 = np.stack([errs[:60], errs[60:120]])
+    mask = (np.arange(120).reshape(2, 60) % 3 != 0).astype(np.float64)
+    assert np.array_equal(O.pck_curve(e2, O.PCK_THRESHOLDS, mask=mask, axis=0), g["pck_axis0_masked"])
+    a = O.aggregate_metrics(recs)
+    text = str(g["summary_text"])
+    assert f"Tracked {a['n_valid']} out of {a['n_total']}, success rate: {a['success_rate']}%" in text
+    assert f"Mean keypoint error: {a['mean_keypoint_error']}" in text
+    assert f"AUC score: {a['auc']}" in text
+    assert f"Mean keypoint accelerations: {a['mean_keypoint_acceleration']}" in text
+    assert f"GT mean keypoint accelerations: {a['gt_mean_keypoint_acceleration']}" in text

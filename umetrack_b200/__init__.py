@@ -26,6 +26,8 @@ def __getattr__(name):
         "mirrored_hand_model": "hand_model", "load_hand_model_from_dict": "hand_model",
         "read_camera_from_json": "cameras", "PinholePlaneCameraModel": "cameras",
         "Fisheye62CameraModel": "cameras", "MetricSums": "metrics",
+        "aggregate_metrics": "aggregate", "save_eval_result": "aggregate", "PCK_curve": "aggregate",
+        "normalized_AUC": "metrics", "PCK_THRESHOLDS": "metrics",
     }
     if name in table:
         return getattr(importlib.import_module(f".{table[name]}", __name__), name)

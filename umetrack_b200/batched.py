@@ -27,7 +27,7 @@ from . import native
 from .cameras import FISHEYE62_FIELDS
 from .hand_model import HandModel, load_hand_model_from_dict, scaled_hand_model
 from .hand_tracker import CONFIDENCE_THRESHOLD, HandTrackerOpts, MM_TO_M, neutral_joint_angles
-from .metrics import MetricSums
+from .metrics import MetricSums, keypoint_errors_device
 from .model import InputFrameDesc, InputSkeletonData
 from .skinning import fk_landmarks_device
 
@@ -207,7 +207,7 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
         pm, gm = pred.reshape(2, T, 21, 3).cpu().numpy(), gt.reshape(2, T, 21, 3).cpu().numpy()
         tk[valid[r]] = pm[valid[r]]
         gk[valid[r]] = gm[valid[r]]
-        err = np.linalg.norm((gk - tk)[valid[r]], axis=-1).mean(axis=-1)
+        err = keypoint_errors_device(pred, gt)[v].cpu().numpy()      # hand-major, like (gt - tracked)[valid]
         results.append({"tracked_keypoints": tk, "gt_keypoints": gk, "valid_tracking": valid[r],
                         "per_frame_mean_error": err})
     return results

@@ -238,6 +238,61 @@ extern "C" int umt_fk_landmarks(const float* axes, const float* rest, const floa
   return umt::check_launch("fk_kernel");
 }
 
+// err[i] = mean over 21 landmarks of |gt - pred|, float64, in numpy's evaluation order:
+// norm = sqrt((dx*dx + dy*dy) + dz*dz); mean = pairwise_sum(21 values) / 21 where pairwise_sum
+// keeps eight partial sums r[j] = a[j] + a[8+j], combines them as ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7))
+// and adds a[16..20] one by one.  No FMA contraction anywhere.  One warp per hand-frame.
+__global__ void __launch_bounds__(256)
+keypoint_error_kernel(const float* __restrict__ pred, const float* __restrict__ gt, int n,
+                      double* __restrict__ err) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int pose = blockIdx.x * 8 + warp; pose < n; pose += gridDim.x * 8) {
+    double d = 0.0;
+    if (lane < UMT_N_LANDMARKS) {
+      const size_t o = ((size_t)pose * UMT_N_LANDMARKS + lane) * 3;
+      const double dx = __dsub_rn((double)gt[o], (double)pred[o]);
+      const double dy = __dsub_rn((double)gt[o + 1], (double)pred[o + 1]);
+      const double dz = __dsub_rn((double)gt[o + 2], (double)pred[o + 2]);
+      d = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+    }
+    // r[j] for j < 8 lives in lane j
+    double r = __dadd_rn(d, __shfl_down_sync(0xffffffffu, d, 8));
+    const double s1 = __dadd_rn(r, __shfl_down_sync(0xffffffffu, r, 1));      // lanes 0,2,4,6: r[j]+r[j+1]
+    const double s2 = __dadd_rn(s1, __shfl_down_sync(0xffffffffu, s1, 2));    // lanes 0,4
+    double res = __dadd_rn(s2, __shfl_down_sync(0xffffffffu, s2, 4));         // lane 0
+    for (int i = 16; i < UMT_N_LANDMARKS; ++i) res = __dadd_rn(res, __shfl_sync(0xffffffffu, d, i));
+    if (lane == 0) err[pose] = __ddiv_rn(res, (double)UMT_N_LANDMARKS);
+  }
+}
+
+// counts[k] += #{i valid : err[i] <= thr[k]}.  Each block histograms "first threshold that
+// admits the error" in shared memory (binary search), then adds the running totals.
+__global__ void __launch_bounds__(256)
+pck_kernel(const double* __restrict__ err, const uint8_t* __restrict__ valid, long long n,
+           const double* __restrict__ thr, int n_thr, double* __restrict__ counts) {
+  __shared__ unsigned int hist[1025];
+  __shared__ double sthr[1024];
+  for (int i = threadIdx.x; i <= n_thr; i += blockDim.x) hist[i] = 0;
+  for (int i = threadIdx.x; i < n_thr; i += blockDim.x) sthr[i] = thr[i];
+  __syncthreads();
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    if (valid && !valid[i]) continue;
+    const double e = err[i];
+    int lo = 0, hi = n_thr;   // first k in [0, n_thr] with e <= thr[k] (n_thr = none; NaN -> none)
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (e <= sthr[mid]) hi = mid; else lo = mid + 1;
+    }
+    atomicAdd(&hist[lo], 1u);
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < n_thr; k += blockDim.x) {
+    unsigned long long c = 0;
+    for (int j = 0; j <= k; ++j) c += hist[j];
+    if (c) atomicAdd(&counts[k], (double)c);
+  }
+}
+
 extern "C" int umt_mpjpe_accumulate(const float* pred, const float* gt, const uint8_t* valid,
                                     int n, double* sums, void* stream) {
   if (n < 0) return umt::fail(UMT_ERR_INVALID, "umt_mpjpe_accumulate: n=%d", n);
@@ -259,4 +314,26 @@ extern "C" int umt_accel_accumulate(const float* pts, const uint8_t* valid, int 
   if (blocks > 148 * 8) blocks = 148 * 8;
   accel_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(pts, valid, n_seq, T, sums);
   return umt::check_launch("accel_kernel");
+}
+
+extern "C" int umt_keypoint_errors(const float* pred, const float* gt, int n, double* err, void* stream) {
+  if (n < 0) return umt::fail(UMT_ERR_INVALID, "umt_keypoint_errors: n=%d", n);
+  if (n == 0) return UMT_OK;
+  if (!pred || !gt || !err) return umt::fail(UMT_ERR_INVALID, "umt_keypoint_errors: null pointer");
+  int blocks = (n + 7) / 8;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  keypoint_error_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(pred, gt, n, err);
+  return umt::check_launch("keypoint_error_kernel");
+}
+
+extern "C" int umt_pck_accumulate(const double* err, const uint8_t* valid, long long n,
+                                  const double* thresholds, int n_thresholds, double* counts, void* stream) {
+  if (n < 0 || n_thresholds < 1 || n_thresholds > 1024)
+    return umt::fail(UMT_ERR_INVALID, "umt_pck_accumulate: n=%lld, n_thresholds=%d (1..1024)", n, n_thresholds);
+  if (n == 0) return UMT_OK;
+  if (!err || !thresholds || !counts) return umt::fail(UMT_ERR_INVALID, "umt_pck_accumulate: null pointer");
+  long long blocks = (n + 255) / 256;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  pck_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(err, valid, n, thresholds, n_thresholds, counts);
+  return umt::check_launch("pck_kernel");
 }

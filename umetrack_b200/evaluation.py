@@ -18,7 +18,7 @@ from .cameras import read_camera_from_json
 from .hand_model import HandModel, NUM_HANDS, NUM_LANDMARKS_PER_HAND, load_hand_model_from_dict, scaled_hand_model
 from .hand_tracker import (HandTracker, HandTrackerOpts, InputFrame, SingleHandPose, ViewData,
                            landmarks_from_poses)
-from .metrics import MetricSums
+from .metrics import MetricSums, keypoint_errors_device
 
 
 class RecordingStream:
@@ -81,12 +81,12 @@ def track_recording(model, labels: dict, frames: np.ndarray, hand_model: Optiona
         lm_gt = landmarks_from_poses(stream.hand_model, ja[n:], wr[n:], hands)
         for k, h in enumerate(hands):
             tracked[h, t], gtk[h, t], valid[h, t] = lm_pred[k], lm_gt[k], True
-    err = np.linalg.norm((gtk - tracked)[valid], axis=-1).mean(axis=-1)
+    dev = sums.device if sums is not None else torch.device("cuda", torch.cuda.current_device())
+    p = torch.from_numpy(tracked.reshape(-1, 21, 3)).float().to(dev)
+    g = torch.from_numpy(gtk.reshape(-1, 21, 3)).float().to(dev)
+    v = torch.from_numpy(valid.reshape(-1)).to(dev)
+    err = keypoint_errors_device(p, g)[v].cpu().numpy()              # run_eval_known_skeleton.py:88-89
     if sums is not None:
-        dev = sums.device
-        p = torch.from_numpy(tracked.reshape(-1, 21, 3)).float().to(dev)
-        g = torch.from_numpy(gtk.reshape(-1, 21, 3)).float().to(dev)
-        v = torch.from_numpy(valid.reshape(-1)).to(dev)
         sums.add_errors(p, g, v)
         sums.add_accelerations(p.reshape(2, T, 21, 3), v.reshape(2, T), gt=False)
         sums.add_accelerations(g.reshape(2, T, 21, 3), v.reshape(2, T), gt=True)

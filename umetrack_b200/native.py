@@ -47,6 +47,8 @@ SIGNATURES = {
     "umt_fk_landmarks": (c_int, [c_void_p] * 8 + [c_int, c_void_p, c_void_p]),
     "umt_mpjpe_accumulate": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_accel_accumulate": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "umt_keypoint_errors": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "umt_pck_accumulate": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int, c_void_p, c_void_p]),
 }
 
 _lib = None
