@@ -48,6 +48,23 @@ def conv_flops_per_crop():
     return out
 
 
+def ncu_conv_traffic(mode):
+    """dram__bytes_read + dram__bytes_write per conv_umma_kernel launch, averaged over the 24
+    backbone launches of the committed `ncu --set full` capture (fp16 mode, 4096 crops per launch);
+    None for the other modes or if the summary is missing.  Bytes per launch, like `achieved`."""
+    path = os.path.join(ROOT, "profiles", "r01_ncu_conv_full_summary_v4.csv")
+    if mode != "fp16" or not os.path.exists(path):
+        return None
+    import csv
+    tot, n = 0.0, 0
+    for r in csv.reader(open(path)):
+        if len(r) > 6 and "conv_umma_kernel<" in r[0] and ", 2, 2>" not in r[0] and ", 0, " not in r[0]:
+            tot += float(r[5]) * 1e9 + float(r[6]) * 1e6   # columns: read [Gbyte], write [Mbyte]
+            n += 1
+    return {"bytes_per_launch": tot / n, "launches": n, "crops_per_launch": 4096,
+            "source": "profiles/r01_ncu_conv_full_summary_v4.csv"} if n else None
+
+
 class ClockSampler:
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -237,6 +254,7 @@ def main():
     ap.add_argument("--mode", default="fp16", choices=["fp32", "bf16", "fp16"],
                     help="encoder numeric mode: fp16 (default; 16-bit operands, fp32 accumulate, parity-tested), "
                          "fp32 (split-bf16 x3, fp32-equivalent) or bf16")
+    ap.add_argument("--chunk", type=int, default=4096, help="crops per encoder pass (workspace size)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -270,7 +288,7 @@ def main():
     K = args.steps
     hm_dict = synthetic.load_hand_model_json(os.path.join(ROOT, "tests", "golden", "generic_hand_model_nomesh.json"))
     hm = hmod.load_hand_model_from_dict(hm_dict)
-    model = UmeTrackModel(synthetic.make_state_dict(0)).to(dev)
+    model = UmeTrackModel(synthetic.make_state_dict(0), chunk_images=args.chunk).to(dev)
     model.set_mode(args.mode)
     host = synthetic.make_model_batch(B, seed=1234 + rank)
     pinned = {k: v.pin_memory() for k, v in host.items()}
@@ -418,7 +436,7 @@ def main():
         executed = achieved * (3 if args.mode == "fp32" else 1)
         line["roofline"] = {
             "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-            "frac": achieved / peak_tf, "traffic": None,
+            "frac": achieved / peak_tf, "traffic": ncu_conv_traffic(args.mode),
             "kernel": "conv_umma_kernel (24 launches per encoder pass)",
             "peak_source": peak_src,
             "note": "achieved = algorithmic conv FLOPs / sum of the 24 launch durations (CUDA events inside "
