@@ -1024,6 +1024,195 @@ stem_kernel(const float* __restrict__ images, int n_img, const float* __restrict
 }
 
 // ------------------------------------------------------------------------------------------
+// Stem on the tensor cores.  A pooled output pixel (oy,ox) sees the 4x4 input patch at rows
+// 2oy-1..2oy+2, columns 2ox-1..2ox+2; the four conv outputs under its 2x2 pooling window are
+// four different 3x3 sub-windows of that patch.  So with K = the 16 patch pixels and
+// N = 4 pool members x 32 channels = 128, ONE M=128,N=128,K=16 MMA evaluates the convolution
+// for 128 pooled pixels (three MMAs in the hi/lo split mode), and the epilogue takes the max
+// over the four 32-column groups, adds the bias, applies ReLU and writes the planar rows.
+// Warp roles: warp 0 issues the MMAs, warps 1-4 build the im2col operand in shared memory
+// (one patch row each), warps 5-8 drain the accumulator; two operand and two accumulator
+// buffers keep the three roles overlapped.
+// ------------------------------------------------------------------------------------------
+constexpr int kStemThreads = 288;
+constexpr int kStemSmem = 1024 + 8192 + 2 * 8192;
+
+template <int MODE>
+__global__ void __launch_bounds__(kStemThreads, 2)
+stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __restrict__ wpack,
+                 const float* __restrict__ bias, FlatTensor out) {
+  constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
+  __shared__ __align__(128) uint8_t smem[kStemSmem];
+  float* s_bias = reinterpret_cast<float*>(smem + 256);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 128);
+  uint8_t* b_smem = smem + 1024;               // [hi|lo][2 planes][128][8] 16-bit
+  uint8_t* a_smem = smem + 1024 + 8192;        // 2 buffers x [hi|lo][2 planes][128 rows][8]
+  const uint32_t bar0 = smem_u32(smem);
+  auto a_full = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+  auto a_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 + i); };
+  auto acc_full = [&](int i) { return bar0 + 8u * (uint32_t)(4 + i); };
+  auto acc_empty = [&](int i) { return bar0 + 8u * (uint32_t)(6 + i); };
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long P = (long long)n_img * 2304;
+  const int n_tiles = (int)((P + 127) / 128);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(a_full(i), 4); mbar_init(a_empty(i), 1); mbar_init(acc_full(i), 1); mbar_init(acc_empty(i), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(256u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  {
+    constexpr int kWBytes = SPLIT ? 8192 : 4096;
+    for (int i = threadIdx.x; i < kWBytes / 16; i += blockDim.x)
+      reinterpret_cast<uint4*>(b_smem)[i] = __ldg(reinterpret_cast<const uint4*>(wpack) + i);
+    if (threadIdx.x < 32) s_bias[threadIdx.x] = bias[threadIdx.x];
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> tensor-core reads
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = (1u << 4) | ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 7) |
+                               ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+    const bool leader = elect_one();
+    const uint32_t b_s = smem_u32(b_smem);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const uint32_t ph = (uint32_t)(it >> 1) & 1u;
+      mbar_wait(acc_empty(buf), ph ^ 1u);
+      mbar_wait(a_full(buf), ph);
+      tc_fence_after();
+      if (leader) {
+        const uint32_t a_s = smem_u32(a_smem + buf * 8192);
+        const uint32_t d = tmem_base + (uint32_t)buf * 128u;
+        tc_mma_bf16(d, umma_desc(a_s, 2048, 128), umma_desc(b_s, 2048, 128), idesc, 0u);
+        if (SPLIT) {
+          tc_mma_bf16(d, umma_desc(a_s, 2048, 128), umma_desc(b_s + 4096, 2048, 128), idesc, 1u);
+          tc_mma_bf16(d, umma_desc(a_s + 4096, 2048, 128), umma_desc(b_s, 2048, 128), idesc, 1u);
+        }
+        tc_commit(a_empty(buf));
+        tc_commit(acc_full(buf));
+      }
+      __syncwarp();
+    }
+  } else if (warp <= 4) {
+    // ===== im2col: one pooled pixel (= one operand row of 16 patch pixels) per thread =====
+    const int r = (warp - 1) * 32 + lane;
+    // the patch of the NEXT tile is requested before the current one is converted and stored
+    auto fetch = [&](int tile, float* px) {
+      const long long p = (long long)tile * 128 + r;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) px[i] = 0.f;
+      if (tile < n_tiles && p < P) {
+        const int img = (int)(p / 2304), rem = (int)(p - (long long)img * 2304), oy = rem / 48, ox = rem - oy * 48;
+        const float* im = images + (size_t)img * 9216;
+#pragma unroll
+        for (int dy = 0; dy < 4; ++dy) {
+          const int yy = 2 * oy + dy - 1;
+#pragma unroll
+          for (int dx = 0; dx < 4; ++dx) {
+            const int xx = 2 * ox + dx - 1;
+            if (yy >= 0 && yy < 96 && xx >= 0 && xx < 96) px[dy * 4 + dx] = __ldg(im + yy * 96 + xx);
+          }
+        }
+      }
+    };
+    float pn[16];
+    fetch(blockIdx.x, pn);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      float px[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) px[i] = pn[i];
+      fetch(tile + (int)gridDim.x, pn);
+      uint4 h[2], l[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float* v = px + 8 * k;
+        if (MODE == UMT_MODE_FP16) {
+          h[k] = make_uint4(pack_f16x2(v[0], v[1]), pack_f16x2(v[2], v[3]), pack_f16x2(v[4], v[5]), pack_f16x2(v[6], v[7]));
+        } else {
+          h[k] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+          if (SPLIT)
+            l[k] = make_uint4(pack_bf16x2(v[0] - bf16_lo(h[k].x), v[1] - bf16_hi(h[k].x)),
+                              pack_bf16x2(v[2] - bf16_lo(h[k].y), v[3] - bf16_hi(h[k].y)),
+                              pack_bf16x2(v[4] - bf16_lo(h[k].z), v[5] - bf16_hi(h[k].z)),
+                              pack_bf16x2(v[6] - bf16_lo(h[k].w), v[7] - bf16_hi(h[k].w)));
+        }
+      }
+      mbar_wait(a_empty(buf), ((uint32_t)(it >> 1) & 1u) ^ 1u);
+      uint8_t* a = a_smem + buf * 8192 + r * 16;
+      *reinterpret_cast<uint4*>(a) = h[0];
+      *reinterpret_cast<uint4*>(a + 2048) = h[1];
+      if (SPLIT) {
+        *reinterpret_cast<uint4*>(a + 4096) = l[0];
+        *reinterpret_cast<uint4*>(a + 6144) = l[1];
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_full(buf));
+    }
+  } else {
+    // ===== epilogue: max over the four pool members, + bias, ReLU, planar rows =====
+    const int lgrp = warp & 3;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const long long p = (long long)tile * 128 + lgrp * 32 + lane;
+      const bool valid = p < P;
+      const int img = (int)(p / 2304), rem = (int)(p - (long long)img * 2304), oy = rem / 48, ox = rem - oy * 48;
+      const long long row = (long long)img * 2401 + oy * 49 + ox;
+      mbar_wait(acc_full(buf), (uint32_t)(it >> 1) & 1u);
+      tc_fence_after();
+      const uint32_t t0 = tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)buf * 128u;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 32; c0 += 16) {
+        uint32_t v0[16], v1[16], v2[16], v3[16];
+        tc_ld16(t0 + c0, v0);
+        tc_ld16(t0 + 32 + c0, v1);
+        tc_ld16(t0 + 64 + c0, v2);
+        tc_ld16(t0 + 96 + c0, v3);
+        tc_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int i = h * 8 + e;
+              const float m = fmaxf(fmaxf(__uint_as_float(v0[i]), __uint_as_float(v1[i])),
+                                    fmaxf(__uint_as_float(v2[i]), __uint_as_float(v3[i])));
+              f[e] = fmaxf(m + s_bias[c0 + i], 0.f);
+            }
+            store_row8<MODE>(out, (c0 >> 3) + h, row, f);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty(buf));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256u) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Projection conv1x1(256->72, bias) (lib/models/model_utils.py:134): planar flat (6x6x256) ->
 // dense float32 [n,72,6,6].  One CTA per image: activations in shared memory, each thread
 // produces one output channel for six pixels (weights read once per six FMAs).
@@ -1370,6 +1559,27 @@ int encoder_build(umt_model* m, const float* const* t) {
   Folded st = folded_from(t, bb + "0.0", bb + "0.1", 32, 1, 3, true);
   m->tw.stem_w = upload(m, st.w);
   m->tw.stem_b = upload(m, st.b);
+  {  // tensor-core stem: B[n = pool member (py,px) * 32 + c][k = patch pixel (dy,dx)] = w[c][dy-py][dx-px]
+    std::vector<uint16_t> bf((size_t)2 * 2 * 128 * 8, 0), h16((size_t)2 * 128 * 8, 0);
+    for (int pp = 0; pp < 4; ++pp)
+      for (int c = 0; c < 32; ++c)
+        for (int k = 0; k < 16; ++k) {
+          const int py = pp >> 1, px = pp & 1, ky = (k >> 2) - py, kx = (k & 3) - px;
+          const float w = (ky >= 0 && ky < 3 && kx >= 0 && kx < 3) ? st.w[(size_t)c * 9 + ky * 3 + kx] : 0.f;
+          const int n = pp * 32 + c;
+          const size_t o = ((size_t)(k >> 3) * 128 + n) * 8 + (k & 7);
+          const uint16_t hi = f2bf(w);
+          bf[o] = hi;
+          bf[(size_t)2 * 128 * 8 + o] = f2bf(w - bf2f(hi));
+          h16[o] = f2h(w);
+        }
+    UMT_CUDA_TRY(cudaMalloc(&m->tw.stem_pack_bf, bf.size() * 2));
+    m->owned.push_back(m->tw.stem_pack_bf);
+    UMT_CUDA_TRY(cudaMemcpy(m->tw.stem_pack_bf, bf.data(), bf.size() * 2, cudaMemcpyHostToDevice));
+    UMT_CUDA_TRY(cudaMalloc(&m->tw.stem_pack_h16, h16.size() * 2));
+    m->owned.push_back(m->tw.stem_pack_h16);
+    UMT_CUDA_TRY(cudaMemcpy(m->tw.stem_pack_h16, h16.data(), h16.size() * 2, cudaMemcpyHostToDevice));
+  }
   Folded pj = folded_from(t, "_feature_extractor._image_backbone.1", "", 72, 256, 1, true);
   {  // the projection also as a tensor-core layer: 1x1, 256 -> 72 (padded to 80), no ReLU, float32 output
     Folded pp;
@@ -1531,7 +1741,16 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
   const long long px = (long long)n_img * 2304;
   const int blocks = (int)((px + 255) / 256);
   if (ev) cudaEventRecord(ev[0], st);
-  if (mode == UMT_MODE_FP32_EQUIV)
+  if (!env_int("UMT_STEM_SIMT", 0)) {
+    const int tiles = (int)((px + 127) / 128);
+    const int grid = std::max(1, std::min(tiles, 2 * sm_count()));
+    if (mode == UMT_MODE_FP32_EQUIV)
+      stem_umma_kernel<UMT_MODE_FP32_EQUIV><<<grid, kStemThreads, 0, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
+    else if (mode == UMT_MODE_BF16)
+      stem_umma_kernel<UMT_MODE_BF16><<<grid, kStemThreads, 0, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
+    else
+      stem_umma_kernel<UMT_MODE_FP16><<<grid, kStemThreads, 0, st>>>(images, n_img, m->tw.stem_pack_h16, m->tw.stem_b, m->buf[0][0]);
+  } else if (mode == UMT_MODE_FP32_EQUIV)
     stem_kernel<UMT_MODE_FP32_EQUIV><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
   else if (mode == UMT_MODE_BF16)
     stem_kernel<UMT_MODE_BF16><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);

@@ -92,6 +92,7 @@ struct TailWeights {
   float *skel_w, *skel_b;                 // [144,132] with BN(4) folded, [144]
   float *head_w[2], *head_b[2];           // [n_out, 80] (zero columns for the channel padding), [n_out]
   float *stem_w, *stem_b;                 // [32,9] folded, [32]
+  uint8_t *stem_pack_bf, *stem_pack_h16;  // tensor-core stem operand [hi|lo][2][128][8] bf16 / [2][128][8] fp16
 };
 
 }  // namespace umt
