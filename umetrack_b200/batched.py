@@ -26,6 +26,7 @@ import torch
 from . import native
 from .cameras import FISHEYE62_FIELDS
 from .hand_model import HandModel, load_hand_model_from_dict, scaled_hand_model
+from .ingest import FrameStager
 from .hand_tracker import CONFIDENCE_THRESHOLD, HandTrackerOpts, MM_TO_M, neutral_joint_angles
 from .metrics import MetricSums, keypoint_errors_device
 from .model import InputFrameDesc, InputSkeletonData
@@ -83,7 +84,8 @@ def crop_cameras_device(hand_model: HandModel, labels: dict, device: torch.devic
 
 
 def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]],
-                             sums: Optional[MetricSums] = None, opts: HandTrackerOpts = HandTrackerOpts()):
+                             sums: Optional[MetricSums] = None, opts: HandTrackerOpts = HandTrackerOpts(),
+                             chunk_frames: int = 32):
     """Known-skeleton tracking of several recordings [(labels, frames uint8 [T,H,n_cam*W]), ...] on
     the current CUDA device.  `frames` is a numpy array or a torch tensor; a tensor in pinned host
     memory is uploaded asynchronously (the upload of the raw frames is the largest single cost of
@@ -96,46 +98,52 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
     lib = native.lib()
     R = len(recordings)
     hand_models = [load_hand_model_from_dict(lab["hand_model"]) for lab, _ in recordings]
-    # ---- 1. crop cameras, 2. resampling ------------------------------------------------------------
-    crops_per_rec, cams_per_rec, counts = [], [], []
+    # ---- 1. crop cameras of every recording (small device work + the host's item lists) ----------------
+    plans, counts = [], []
     for (lab, frames), hm in zip(recordings, hand_models):
         cc = crop_cameras_device(hm, lab, dev, opts, min_num_crops=1)
         T, H, W4 = frames.shape
-        n_cam = len(lab["cameras"])
-        W = W4 // n_cam
+        W = W4 // len(lab["cameras"])
         cnt = cc["sel_count"].cpu().numpy()                      # [T,2]
         sel = cc["sel_cam"].cpu().numpy()                        # [T,2,2]
         # crops are stored frame major, hand minor, view minor-most
         t_i, h_i, k_i = np.nonzero(np.arange(sel.shape[2])[None, None, :] < cnt[:, :, None])
-        item = t_i
-        if len(item):
+        plan = {"t_i": t_i, "H": H, "W": W, "W4": W4}
+        if len(t_i):
             thk = torch.from_numpy(np.stack([t_i, h_i, k_i])).to(dev)
             ti, hi, ki = thk[0], thk[1], thk[2]
-            params = cc["resample_params"][ti, hi, ki].contiguous()
-            offs = torch.from_numpy(t_i.astype(np.int64) * (H * W4) + sel[t_i, h_i, k_i].astype(np.int64) * W).to(dev)
-            if isinstance(frames, torch.Tensor):
-                src = frames.contiguous().to(dev, non_blocking=True)
-            else:
-                src = torch.from_numpy(np.ascontiguousarray(frames)).to(dev)
-            crops = torch.empty((len(item), 96, 96), dtype=torch.float32, device=dev)
-            native.check(lib.umt_resample_crops(native.ptr(src), native.ptr(offs), W4, W, H, native.ptr(params),
-                                                len(item), 0, native.ptr(crops), 0, native.current_stream_ptr()),
-                         "umt_resample_crops")
-            intr = cc["intrinsics"][ti, hi, ki].contiguous()
-            extr = cc["extrinsics"][ti, hi, ki].contiguous()
-        else:
-            crops = torch.empty((0, 96, 96), device=dev)
-            intr = torch.empty((0, 3, 3), device=dev)
-            extr = torch.empty((0, 4, 4), device=dev)
-        crops_per_rec.append(crops)
-        cams_per_rec.append((intr, extr, item))
+            plan["params"] = cc["resample_params"][ti, hi, ki].contiguous()
+            # offset of each item's source view inside its staging chunk
+            plan["offs"] = torch.from_numpy((t_i % chunk_frames).astype(np.int64) * (H * W4)
+                                            + sel[t_i, h_i, k_i].astype(np.int64) * W).to(dev)
+            plan["intr"] = cc["intrinsics"][ti, hi, ki]
+            plan["extr"] = cc["extrinsics"][ti, hi, ki]
+        plans.append(plan)
         counts.append(cnt)
+    base = np.cumsum([0] + [len(pl["t_i"]) for pl in plans])
+    # ---- 2. resampling: frames go up in chunks through the staging ring (the upload of chunk k+1
+    # overlaps the resampling of chunk k; the host only enqueues here, so uploads run back to back
+    # across recordings); items are frame-major, so a chunk's items are contiguous ---------------------
+    all_crops = torch.empty((int(base[-1]), 96, 96), dtype=torch.float32, device=dev)
+    stager = FrameStager(dev, chunk_frames=chunk_frames)
+    for r, ((lab, frames), pl) in enumerate(zip(recordings, plans)):
+        t_i = pl["t_i"]
+        if not len(t_i):
+            continue
+        for t0, t1, chunk, slot in stager.chunks(frames):
+            i0, i1 = (int(v) for v in np.searchsorted(t_i, [t0, t1]))
+            if i1 > i0:
+                native.check(lib.umt_resample_crops(
+                    chunk.data_ptr(), pl["offs"].data_ptr() + 8 * i0, pl["W4"], pl["W"], pl["H"],
+                    pl["params"].data_ptr() + 8 * 48 * i0, i1 - i0, 0,
+                    all_crops.data_ptr() + 4 * 9216 * (int(base[r]) + i0), 0, native.current_stream_ptr()),
+                    "umt_resample_crops")
+            stager.release(slot)
     # ---- 3. backbone over every crop of every recording ---------------------------------------------
-    all_crops = torch.cat(crops_per_rec, dim=0)
     feats = model.encode(all_crops) if len(all_crops) else torch.empty((0, 72, 6, 6), device=dev)
-    all_intr = torch.cat([c[0] for c in cams_per_rec], dim=0)
-    all_extr = torch.cat([c[1] for c in cams_per_rec], dim=0)
-    base = np.cumsum([0] + [len(c) for c in crops_per_rec])
+    with_items = [pl for pl in plans if len(pl["t_i"])]
+    all_intr = torch.cat([pl["intr"] for pl in with_items], dim=0) if with_items else torch.empty((0, 3, 3), device=dev)
+    all_extr = torch.cat([pl["extr"] for pl in with_items], dim=0) if with_items else torch.empty((0, 4, 4), device=dev)
     # crop index ranges per (recording, frame, hand): crops are stored frame major, hand minor
     start = []
     for r in range(R):
