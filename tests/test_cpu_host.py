@@ -145,3 +145,64 @@ def test_metric_sums_all_reduce_gloo_world_size_2(tmp_path):
     outs = [p.communicate(timeout=120)[0].decode() for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert all("ok" in o for o in outs)
+
+
+def test_torch_data_reader_matches_reference_parser(tmp_path):
+    """the committed idx/bin files, as parsed by the reference when the goldens
+    were made (tests/golden/make_torchdata_reader_golden.py), vs our reader; plus error cases."""
+    from umetrack_b200.torch_data_reader import (MAGIC, SequenceFolder, TorchIdx, find_sequence_folders,
+                                                  parse_raw_buffers, write_torch_idx_bin)
+
+    gdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g = np.load(os.path.join(gdir, "torchdata_reader_golden.npz"))
+    folder = os.path.join(gdir, "torchdata_seq")
+    assert find_sequence_folders(gdir) == [folder]
+    ds = SequenceFolder(folder)
+    assert len(ds) == int(g["n"])
+    mono_idx = TorchIdx(os.path.join(folder, "mono.torch.idx"))
+    assert mono_idx.is_uniform == bool(g["mono_is_uniform"]) and mono_idx.shape is None
+    with pytest.raises(ValueError):
+        mono_idx.item_shape()
+    for i in range(len(ds)):
+        item = ds[i]
+        assert item["mono"].dtype == np.uint8 and np.array_equal(item["mono"], g[f"mono_{i}"])
+        assert tuple(g[f"mono_dims_{i}"]) == mono_idx.item_shape(i)
+        assert int(g[f"mono_offset_{i}"]) == mono_idx.byte_offset(i)
+        s = parse_raw_buffers(**item)
+        for f in ("extrinsics", "intrinsics", "enclosing_points", "hand", "wrist", "joint_angles",
+                  "solved_wrist_xfs", "solved_joint_angles", "pinch"):
+            v = getattr(s, f)
+            assert v.dtype == np.float32 and np.array_equal(v, g[f"{f}_{i}"]), f
+        assert np.array_equal(s.hand_model.joint_rest_positions.numpy(), g[f"hm_rest_{i}"])
+        assert float(s.hand_model.hand_scale) == float(g[f"hm_scale_{i}"])
+        s.scaled(0.001)
+        assert np.array_equal(s.extrinsics, g[f"scaled_extrinsics_{i}"])
+        assert np.array_equal(s.hand_model.joint_rest_positions.numpy(), g[f"scaled_hm_rest_{i}"])
+    uni = TorchIdx(os.path.join(folder, "uniform.torch.idx"))
+    assert uni.shape == tuple(g["uniform_shape"]) and np.array_equal(uni.read_bin(), g["uniform_data"])
+    assert uni.item_shape() == (2, 3) and uni.data_size_bytes() == 4 * 6 * 4
+    # round trip + the reference's error behaviour
+    p = str(tmp_path / "x.torch.idx")
+    write_torch_idx_bin(p, [np.arange(6, dtype=np.int16).reshape(2, 3), np.arange(4, dtype=np.int16)], dtype="int16")
+    idx = TorchIdx(p)
+    assert not idx.is_uniform and np.array_equal(idx.read_item(1), np.arange(4))
+    with pytest.raises(IndexError):
+        idx.read_item(2)
+    raw = np.fromfile(p, dtype=np.int64)
+    for pos, val, exc in ((0, 123, ValueError), (1, 7, ValueError), (2, 99, KeyError), (3, 4, ValueError)):
+        bad = raw.copy()
+        bad[pos] = val
+        with pytest.raises(exc):
+            TorchIdx(p, buffer=bad.tobytes())
+    with pytest.raises(ValueError):
+        TorchIdx(p, buffer=raw.tobytes()[:-3])
+    with pytest.raises(ValueError):
+        idx.view_frame(0, b"123")
+    assert raw[0] == MAGIC and raw[1] == 1
+    with pytest.raises(ValueError):
+        SequenceFolder(str(tmp_path), fields=("mono",))                       # missing field
+    write_torch_idx_bin(str(tmp_path / "a.torch.idx"), [np.zeros(2, dtype=np.uint8)], dtype="uint8")
+    with pytest.raises(ValueError):
+        SequenceFolder(str(tmp_path), fields=("x", "a"))                      # 2 items vs 1
+    with pytest.raises(TypeError):
+        parse_raw_buffers(np.zeros(1), {"unknown_field": [1.0]})

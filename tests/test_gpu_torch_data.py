@@ -60,3 +60,51 @@ def test_homography_argument_validation():
     assert lib.umt_resample_homography(0, 8, 8, 0, 0, 96, 96, 0, 0, 0) == 0     # n = 0
     assert lib.umt_resample_homography(0, 8, 8, 0, 1, 97, 96, 0, 0, 0) != 0     # out_w % 4
     assert lib.umt_resample_homography(0, 1, 8, 0, 1, 96, 96, 0, 0, 0) != 0     # degenerate source
+
+
+def test_sequence_folder_end_to_end_against_oracle():
+    """idx/bin folder -> parse -> GPU crops -> model stepped over the sequence
+    (run_inference_torch_data.py:39-133), against the oracle fed the same prepared inputs."""
+    import os
+
+    from tests.helpers import GOLDEN
+    from umetrack_b200.model import UmeTrackModel
+    from umetrack_b200.torch_data_reader import SequenceFolder, eval_sequences, parse_raw_buffers, prepare_model_inputs
+
+    ds = SequenceFolder(os.path.join(GOLDEN, "torchdata_seq"))
+    sd = synthetic.make_state_dict(0)
+    model = UmeTrackModel(sd).to("cuda")
+    for i in range(len(ds)):
+        raw = ds[i]
+        inp = prepare_model_inputs(parse_raw_buffers(**raw), (96, 96))
+        seq = raw["mono"].shape[0]
+        assert inp["left_images"].shape == (seq, 2, 96, 96) and float(inp["left_images"].max()) <= 1.0
+        # crops: same as calling the crop function directly on the (scaled) sample
+        s2 = parse_raw_buffers(**ds[i])
+        s2.scaled(0.001)
+        crops, ex, kk = perspective_crop_images(s2.images.astype(np.float32), s2.extrinsics, s2.intrinsics,
+                                                s2.enclosing_points, int(s2.hand[0]), (96, 96))
+        assert np.array_equal(crops, inp["left_images"].numpy()) and np.array_equal(ex, inp["extrinsics_xf"].numpy())
+        err_mm, ja, wr = eval_sequences(model, [inp])
+        # oracle: same stepping on the CPU
+        orc = O.OracleModel(sd)
+        hm = inp["left_hand_model"]
+        kp_o, kp_g = [], []
+        for t in range(seq):
+            ref = orc.regress_pose_use_skeleton(
+                inp["left_images"][t], inp["intrinsics"][t], inp["extrinsics_xf"][t], torch.tensor([[0, 2]]),
+                torch.tensor([0]), torch.tensor([t > 0]), inp["hand_idx"][t:t + 1].long(),
+                hm.joint_rotation_axes[t][None], hm.joint_rest_positions[t][None])
+            un = [hm.joint_rotation_axes[t].clone(), hm.joint_rest_positions[t].clone(), hm.landmark_rest_positions[t].clone()]
+            if int(inp["hand_idx"][t]) == 1:      # un-mirror (lib/common/hand.py:101-134)
+                un[0][:, 1:] *= -1
+                un[1][:, 0] *= -1
+                un[2][:, 0] *= -1
+            args = (un[0], un[1], un[2], hm.landmark_rest_bone_indices[t], hm.landmark_rest_bone_weights[t])
+            kp_o.append(O.skin_landmarks(*args, ref["joint_angles"], ref["wrist_xfs"]))
+            kp_g.append(O.skin_landmarks(*args, inp["joint_angles"][t:t + 1], inp["wrist_xfs"][t:t + 1]))
+            d_ja = float((ja[0, t].cpu() - ref["joint_angles"][0]).abs().max())
+            assert d_ja < 2e-4, (i, t, d_ja)
+        kp_o, kp_g = torch.cat(kp_o), torch.cat(kp_g)
+        want = float((kp_g - kp_o).norm(dim=-1).mean() * 1000)
+        assert abs(float(err_mm[0]) - want) < 0.01, (float(err_mm[0]), want)
