@@ -1035,14 +1035,16 @@ stem_kernel(const float* __restrict__ images, int n_img, const float* __restrict
 // buffers keep the three roles overlapped.
 // ------------------------------------------------------------------------------------------
 constexpr int kStemThreads = 288;
-constexpr int kStemSmem = 1024 + 8192 + 2 * 8192;
+constexpr int kStemDepth = 6;                                  // staging tiles in flight per CTA
+constexpr int kStemStageOff = 1024 + 8192 + 2 * 8192;
+constexpr int kStemSmem = kStemStageOff + kStemDepth * 8192;   // dynamic shared memory
 
 template <int MODE>
 __global__ void __launch_bounds__(kStemThreads, 2)
 stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __restrict__ wpack,
                  const float* __restrict__ bias, FlatTensor out) {
   constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
-  __shared__ __align__(128) uint8_t smem[kStemSmem];
+  extern __shared__ __align__(128) uint8_t smem[];
   float* s_bias = reinterpret_cast<float*>(smem + 256);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 128);
   uint8_t* b_smem = smem + 1024;               // [hi|lo][2 planes][128][8] 16-bit
@@ -1108,34 +1110,40 @@ stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __r
   } else if (warp <= 4) {
     // ===== im2col: one pooled pixel (= one operand row of 16 patch pixels) per thread =====
     const int r = (warp - 1) * 32 + lane;
-    // the patch of the NEXT tile is requested before the current one is converted and stored
-    auto fetch = [&](int tile, float* px) {
+    // The patch pixels travel global -> shared with 4-byte cp.async into a ring of kStemDepth
+    // staging tiles ([16 pixels][128 rows] float, zero-filled outside the image), so the loads of
+    // several tiles are in flight without holding registers; each thread only ever reads back
+    // the row it requested itself, so cp.async.wait_group is all the synchronisation needed.
+    float* stage = reinterpret_cast<float*>(smem + kStemStageOff);
+    auto request = [&](int tile, int slot) {
       const long long p = (long long)tile * 128 + r;
+      const bool ok = tile < n_tiles && p < P;
+      const int img = ok ? (int)(p / 2304) : 0;
+      const int rem = ok ? (int)(p - (long long)img * 2304) : 0, oy = rem / 48, ox = rem - oy * 48;
+      const float* im = images + (size_t)img * 9216;
+      const uint32_t dst0 = smem_u32(stage + (size_t)slot * 2048 + r);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) px[i] = 0.f;
-      if (tile < n_tiles && p < P) {
-        const int img = (int)(p / 2304), rem = (int)(p - (long long)img * 2304), oy = rem / 48, ox = rem - oy * 48;
-        const float* im = images + (size_t)img * 9216;
+      for (int dy = 0; dy < 4; ++dy) {
+        const int yy = 2 * oy + dy - 1;
 #pragma unroll
-        for (int dy = 0; dy < 4; ++dy) {
-          const int yy = 2 * oy + dy - 1;
-#pragma unroll
-          for (int dx = 0; dx < 4; ++dx) {
-            const int xx = 2 * ox + dx - 1;
-            if (yy >= 0 && yy < 96 && xx >= 0 && xx < 96) px[dy * 4 + dx] = __ldg(im + yy * 96 + xx);
-          }
+        for (int dx = 0; dx < 4; ++dx) {
+          const int xx = 2 * ox + dx - 1;
+          const bool in = ok && yy >= 0 && yy < 96 && xx >= 0 && xx < 96;
+          const float* src = in ? im + yy * 96 + xx : images;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + (uint32_t)(dy * 4 + dx) * 512u),
+                       "l"(src), "r"(in ? 4u : 0u) : "memory");
         }
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    float pn[16];
-    fetch(blockIdx.x, pn);
+    for (int d = 0; d < kStemDepth; ++d) request(blockIdx.x + d * (int)gridDim.x, d);
     int it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const int buf = it & 1;
+      const int buf = it & 1, slot = it % kStemDepth;
+      asm volatile("cp.async.wait_group %0;" ::"n"(kStemDepth - 1) : "memory");
       float px[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) px[i] = pn[i];
-      fetch(tile + (int)gridDim.x, pn);
+      for (int i = 0; i < 16; ++i) px[i] = stage[(size_t)slot * 2048 + i * 128 + r];
       uint4 h[2], l[2];
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
@@ -1151,6 +1159,7 @@ stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __r
                               pack_bf16x2(v[6] - bf16_lo(h[k].w), v[7] - bf16_hi(h[k].w)));
         }
       }
+      request(tile + kStemDepth * (int)gridDim.x, slot);   // refill the staging slot just consumed
       mbar_wait(a_empty(buf), ((uint32_t)(it >> 1) & 1u) ^ 1u);
       uint8_t* a = a_smem + buf * 8192 + r * 16;
       *reinterpret_cast<uint4*>(a) = h[0];
@@ -1744,12 +1753,19 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
   if (!env_int("UMT_STEM_SIMT", 0)) {
     const int tiles = (int)((px + 127) / 128);
     const int grid = std::max(1, std::min(tiles, 2 * sm_count()));
+    static bool attr_done = false;
+    if (!attr_done) {
+      UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP32_EQUIV>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+      UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+      UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+      attr_done = true;
+    }
     if (mode == UMT_MODE_FP32_EQUIV)
-      stem_umma_kernel<UMT_MODE_FP32_EQUIV><<<grid, kStemThreads, 0, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
+      stem_umma_kernel<UMT_MODE_FP32_EQUIV><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
     else if (mode == UMT_MODE_BF16)
-      stem_umma_kernel<UMT_MODE_BF16><<<grid, kStemThreads, 0, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
+      stem_umma_kernel<UMT_MODE_BF16><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
     else
-      stem_umma_kernel<UMT_MODE_FP16><<<grid, kStemThreads, 0, st>>>(images, n_img, m->tw.stem_pack_h16, m->tw.stem_b, m->buf[0][0]);
+      stem_umma_kernel<UMT_MODE_FP16><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_h16, m->tw.stem_b, m->buf[0][0]);
   } else if (mode == UMT_MODE_FP32_EQUIV)
     stem_kernel<UMT_MODE_FP32_EQUIV><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
   else if (mode == UMT_MODE_BF16)
