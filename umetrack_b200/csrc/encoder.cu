@@ -1858,13 +1858,13 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
   if (!env_int("UMT_STEM_SIMT", 0)) {
     const int tiles = (int)((px + 127) / 128);
     const int grid = std::max(1, std::min(tiles, 2 * sm_count()));
-    static bool attr_done = false;
-    if (!attr_done) {
+    // (per launch, like launch_conv_t: the attribute belongs to the current device)
+    if (mode == UMT_MODE_FP32_EQUIV)
       UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP32_EQUIV>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+    else if (mode == UMT_MODE_BF16)
       UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+    else
       UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
-      attr_done = true;
-    }
     if (mode == UMT_MODE_FP32_EQUIV)
       stem_umma_kernel<UMT_MODE_FP32_EQUIV><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
     else if (mode == UMT_MODE_BF16)
