@@ -92,7 +92,9 @@ __device__ __forceinline__ PixelCoord quantise(float mx, float my) {
   return c;
 }
 
-__global__ void __launch_bounds__(kThreads)
+// four CTAs per SM (64 registers): the float64 chain is latency bound, so occupancy -- not
+// per-thread ILP -- sets the rate (1 CTA/SM at 139 registers ran 2.3x slower)
+__global__ void __launch_bounds__(kThreads, 4)
 resample_kernel(const uint8_t* __restrict__ src_base, const int64_t* __restrict__ src_offset,
                 int src_pitch, int src_w, int src_h, const double* __restrict__ params,
                 uint8_t* __restrict__ out_u8, float* __restrict__ out_f32,
