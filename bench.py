@@ -52,17 +52,20 @@ def ncu_conv_traffic(mode):
     """dram__bytes_read + dram__bytes_write per conv_umma_kernel launch, averaged over the 24
     backbone launches of the committed `ncu --set full` capture (fp16 mode, 4096 crops per launch);
     None for the other modes or if the summary is missing.  Bytes per launch, like `achieved`."""
-    path = os.path.join(ROOT, "profiles", "r01_ncu_conv_full_summary_v4.csv")
+    path = os.path.join(ROOT, "profiles", "r01_ncu_conv_full_summary_v5.csv")
     if mode != "fp16" or not os.path.exists(path):
         return None
     import csv
     tot, n = 0.0, 0
     for r in csv.reader(open(path)):
-        if len(r) > 6 and "conv_umma_kernel<" in r[0] and ", 2, 2>" not in r[0] and ", 0, " not in r[0]:
+        if len(r) <= 6 or "conv_umma_kernel<" not in r[0]:
+            continue
+        targs = [int(v) for v in r[0].split("<")[1].split(">")[0].replace("true", "1").replace("false", "0").split(",")]
+        if targs[0] in (32, 64, 128, 256) and targs[1] == 2 and targs[2] != 2:     # backbone, fp16 mode
             tot += float(r[5]) * 1e9 + float(r[6]) * 1e6   # columns: read [Gbyte], write [Mbyte]
             n += 1
     return {"bytes_per_launch": tot / n, "launches": n, "crops_per_launch": 4096,
-            "source": "profiles/r01_ncu_conv_full_summary_v4.csv"} if n else None
+            "source": "profiles/r01_ncu_conv_full_summary_v5.csv"} if n else None
 
 
 class ClockSampler:
