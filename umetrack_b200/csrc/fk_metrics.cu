@@ -1,11 +1,11 @@
 // Stage (c): forward kinematics + linear-blend skinning of the 21 landmarks, and the
 // MPJPE / keypoint-acceleration reductions (see include/umetrack_b200.h).
 //
-// FK: one thread per hand pose (clamped-angle Rodrigues per joint, lib/common/hand_skinning.py:
-// 35-53; the five 4-joint finger chains, :17-32,100-127; linear-blend skinning of the 21
-// landmarks, :56-97,130-186), 128 poses per CTA with a shared output tile for coalesced stores.
-// The metric kernels use one warp per pose and finish with a shuffle reduction and one float64
-// atomic per CTA.
+// Warp-level kernels: one warp owns one hand pose.  Lanes 0..19 build the 20 finger-joint local
+// transforms (clamped-angle Rodrigues, lib/common/hand_skinning.py:35-53), lanes 0..4 walk the
+// five 4-joint finger chains (hand_skinning.py:17-32,100-127), lanes 0..20 blend one landmark
+// each (hand_skinning.py:56-97,130-186).  The metric kernels also use one warp per pose and
+// finish with a shuffle reduction and one float64 atomic per CTA.
 #include "common.cuh"
 
 namespace {
@@ -32,131 +32,105 @@ __device__ __forceinline__ Xf compose(const Xf& a, const Xf& b) {
   return c;
 }
 
-// One THREAD per hand pose, 128 poses per CTA.  (The first version used one warp per pose; with
-// 5 of 32 lanes busy in the finger chains it issued ~600 warp instructions per pose and reached
-// 10 % of the HBM rate.)  Each thread walks the five 4-joint chains in registers; whenever a
-// skinning frame is complete it is applied to the landmarks that reference it, through a
-// per-frame list of (landmark, weight) entries that the CTA builds once in shared memory with
-// the reference's "later entry overwrites" rule (hand_skinning.py:87-94).  Landmarks accumulate
-// in a shared [pose][63] tile (row stride 63 words: conflict free), which is finally written out
-// with fully coalesced stores; the hand-model constants are shared-memory broadcasts.
-constexpr int kFkPoses = 128;
-
-struct FkShared {
-  float axes[20 * 3], rest[20 * 3], lm[21 * 3];
-  float ent_w[64];
-  int ent_lm[64];
-  int ent_first[18];          // entries of frame f: [ent_first[f], ent_first[f+1])
-  float out[kFkPoses * 63];
-};
-
-__device__ __forceinline__ void fk_apply(const FkShared& S, const Xf& T, int frame, float* __restrict__ o) {
-  for (int e = S.ent_first[frame]; e < S.ent_first[frame + 1]; ++e) {
-    const int l = S.ent_lm[e];
-    const float w = S.ent_w[e];
-    const float wx = S.lm[l * 3 + 0] * w, wy = S.lm[l * 3 + 1] * w, wz = S.lm[l * 3 + 2] * w;
-    o[l * 3 + 0] += T.m[0] * wx + T.m[1] * wy + T.m[2] * wz + T.m[3] * w;
-    o[l * 3 + 1] += T.m[4] * wx + T.m[5] * wy + T.m[6] * wz + T.m[7] * w;
-    o[l * 3 + 2] += T.m[8] * wx + T.m[9] * wy + T.m[10] * wz + T.m[11] * w;
-  }
-}
-
-__global__ void __launch_bounds__(kFkPoses)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
 fk_kernel(const float* __restrict__ axes, const float* __restrict__ rest,
           const float* __restrict__ lm_rest, const float* __restrict__ lm_idx,
           const float* __restrict__ lm_w, const float* __restrict__ joint_angles,
           const float* __restrict__ wrist, const uint8_t* __restrict__ mirror, int n,
           float* __restrict__ out) {
-  extern __shared__ __align__(16) uint8_t fk_smem[];
-  FkShared& S = *reinterpret_cast<FkShared*>(fk_smem);
-  const int t = threadIdx.x;
-  if (t < 60) { S.axes[t] = axes[t]; S.rest[t] = rest[t]; }
-  if (t < 63) S.lm[t] = lm_rest[t];
-  if (t == 64) {
-    // effective skinning weights: non-zero weights scattered into a [21,17] matrix, a later
-    // entry with the same bone index overwriting an earlier one; listed per frame
-    int n_ent = 0;
-    for (int f = 0; f < 17; ++f) {
-      S.ent_first[f] = n_ent;
-      for (int l = 0; l < UMT_N_LANDMARKS; ++l) {
-        float w = 0.f;
-        bool hit = false;
-        for (int k = 0; k < 3; ++k) {
-          const float wk = lm_w[l * 3 + k];
-          if (wk != 0.f && (int)lm_idx[l * 3 + k] == f) { w = wk; hit = true; }
-        }
-        if (hit && n_ent < 64) { S.ent_lm[n_ent] = l; S.ent_w[n_ent] = w; ++n_ent; }
-      }
-    }
-    S.ent_first[17] = n_ent;
-  }
-  float* o = S.out + t * 63;
-#pragma unroll
-  for (int i = 0; i < 63; ++i) o[i] = 0.f;
-  __syncthreads();
+  __shared__ Xf sLocal[kWarpsPerBlock][20];
+  __shared__ Xf sFrame[kWarpsPerBlock][17];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int pose = blockIdx.x * kWarpsPerBlock + warp;
+  if (pose >= n) return;
 
-  const long long pose = (long long)blockIdx.x * kFkPoses + t;
-  if (pose < n) {
-    // wrist transform (root and wrist frames share it); right hands flip column 0
-    Xf W;
-    {
-      const float4* w4 = reinterpret_cast<const float4*>(wrist + (size_t)pose * 16);
-      const float sgn = (mirror && mirror[pose]) ? -1.0f : 1.0f;
+  // wrist transform (root and wrist frames share it); right hands flip column 0
+  Xf W;
+  {
+    const float* w = wrist + (size_t)pose * 16;
+    const float sgn = (mirror && mirror[pose]) ? -1.0f : 1.0f;
 #pragma unroll
-      for (int i = 0; i < 3; ++i) {
-        const float4 r = __ldg(w4 + i);
-        W.m[i * 4 + 0] = r.x * sgn; W.m[i * 4 + 1] = r.y; W.m[i * 4 + 2] = r.z; W.m[i * 4 + 3] = r.w;
-      }
-    }
-    fk_apply(S, W, 0, o);
-    fk_apply(S, W, 1, o);
-    const float* ja = joint_angles + (size_t)pose * UMT_N_JOINTS;
-#pragma unroll 1
-    for (int f = 0; f < 5; ++f) {
-      Xf cur = W;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int jt = 4 * f + j;
-        // clamped-angle Rodrigues (pytorch3d so3_exp_map) and t = p - R p (hand_skinning.py:35-53)
-        const float a = __ldg(ja + jt);
-        const float vx = S.axes[jt * 3 + 0] * a, vy = S.axes[jt * 3 + 1] * a, vz = S.axes[jt * 3 + 2] * a;
-        const float nrm2 = fmaxf(vx * vx + vy * vy + vz * vz, 1e-4f);
-        const float th = sqrtf(nrm2);
-        const float f1 = sinf(th) / th;
-        const float f2 = (1.0f - cosf(th)) / (th * th);
-        const float k2xx = -(vy * vy + vz * vz), k2yy = -(vx * vx + vz * vz), k2zz = -(vx * vx + vy * vy);
-        const float k2xy = vx * vy, k2xz = vx * vz, k2yz = vy * vz;
-        float R[9];
-        R[0] = 1.0f + f2 * k2xx;
-        R[1] = f1 * (-vz) + f2 * k2xy;
-        R[2] = f1 * (vy) + f2 * k2xz;
-        R[3] = f1 * (vz) + f2 * k2xy;
-        R[4] = 1.0f + f2 * k2yy;
-        R[5] = f1 * (-vx) + f2 * k2yz;
-        R[6] = f1 * (-vy) + f2 * k2xz;
-        R[7] = f1 * (vx) + f2 * k2yz;
-        R[8] = 1.0f + f2 * k2zz;
-        const float rx = S.rest[jt * 3 + 0], ry = S.rest[jt * 3 + 1], rz = S.rest[jt * 3 + 2];
-        Xf L;
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-          L.m[i * 4 + 0] = R[i * 3 + 0];
-          L.m[i * 4 + 1] = R[i * 3 + 1];
-          L.m[i * 4 + 2] = R[i * 3 + 2];
-          const float rr = (i == 0) ? rx : (i == 1 ? ry : rz);
-          L.m[i * 4 + 3] = rr - (R[i * 3 + 0] * rx + R[i * 3 + 1] * ry + R[i * 3 + 2] * rz);
-        }
-        cur = compose(cur, L);
-        if (j >= 1) fk_apply(S, cur, 2 + 3 * f + (j - 1), o);   // frames: [wrist, wrist, per finger: after joints 1, 2, 3]
-      }
+    for (int i = 0; i < 3; ++i) {
+      W.m[i * 4 + 0] = w[i * 4 + 0] * sgn;
+      W.m[i * 4 + 1] = w[i * 4 + 1];
+      W.m[i * 4 + 2] = w[i * 4 + 2];
+      W.m[i * 4 + 3] = w[i * 4 + 3];
     }
   }
-  __syncthreads();
-  // coalesced copy of this CTA's [poses][63] tile
-  const long long base = (long long)blockIdx.x * kFkPoses * 63;
-  const long long total = (long long)n * 63;
-  for (int i = t; i < kFkPoses * 63; i += kFkPoses)
-    if (base + i < total) out[base + i] = S.out[i];
+  if (lane < 20) {
+    const float a = joint_angles[(size_t)pose * UMT_N_JOINTS + lane];
+    const float vx = axes[lane * 3 + 0] * a, vy = axes[lane * 3 + 1] * a, vz = axes[lane * 3 + 2] * a;
+    const float nrm2 = fmaxf(vx * vx + vy * vy + vz * vz, 1e-4f);
+    const float th = sqrtf(nrm2);
+    const float f1 = sinf(th) / th;
+    const float f2 = (1.0f - cosf(th)) / (th * th);
+    // K = hat(v), K2 = K*K
+    const float k2xx = -(vy * vy + vz * vz), k2yy = -(vx * vx + vz * vz), k2zz = -(vx * vx + vy * vy);
+    const float k2xy = vx * vy, k2xz = vx * vz, k2yz = vy * vz;
+    float R[9];
+    R[0] = 1.0f + f2 * k2xx;
+    R[1] = f1 * (-vz) + f2 * k2xy;
+    R[2] = f1 * (vy) + f2 * k2xz;
+    R[3] = f1 * (vz) + f2 * k2xy;
+    R[4] = 1.0f + f2 * k2yy;
+    R[5] = f1 * (-vx) + f2 * k2yz;
+    R[6] = f1 * (-vy) + f2 * k2xz;
+    R[7] = f1 * (vx) + f2 * k2yz;
+    R[8] = 1.0f + f2 * k2zz;
+    const float rx = rest[lane * 3 + 0], ry = rest[lane * 3 + 1], rz = rest[lane * 3 + 2];
+    Xf L;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      L.m[i * 4 + 0] = R[i * 3 + 0];
+      L.m[i * 4 + 1] = R[i * 3 + 1];
+      L.m[i * 4 + 2] = R[i * 3 + 2];
+      const float rr = (i == 0) ? rx : (i == 1 ? ry : rz);
+      L.m[i * 4 + 3] = rr - (R[i * 3 + 0] * rx + R[i * 3 + 1] * ry + R[i * 3 + 2] * rz);
+    }
+    sLocal[warp][lane] = L;
+  }
+  __syncwarp();
+  if (lane < 5) {
+    Xf cur = compose(W, sLocal[warp][4 * lane + 0]);
+    cur = compose(cur, sLocal[warp][4 * lane + 1]);
+    sFrame[warp][2 + 3 * lane + 0] = cur;
+    cur = compose(cur, sLocal[warp][4 * lane + 2]);
+    sFrame[warp][2 + 3 * lane + 1] = cur;
+    cur = compose(cur, sLocal[warp][4 * lane + 3]);
+    sFrame[warp][2 + 3 * lane + 2] = cur;
+  } else if (lane == 5) {
+    sFrame[warp][0] = W;
+    sFrame[warp][1] = W;
+  }
+  __syncwarp();
+  if (lane < UMT_N_LANDMARKS) {
+    const float px = lm_rest[lane * 3 + 0], py = lm_rest[lane * 3 + 1], pz = lm_rest[lane * 3 + 2];
+    int bi[3];
+    float bw[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      bi[k] = (int)lm_idx[lane * 3 + k];
+      bw[k] = lm_w[lane * 3 + k];
+    }
+    // the reference scatters non-zero weights into a [21,17] matrix: a later entry with the same
+    // bone index overwrites an earlier one (hand_skinning.py:87-94)
+    if (bw[0] != 0.f && ((bw[1] != 0.f && bi[1] == bi[0]) || (bw[2] != 0.f && bi[2] == bi[0]))) bw[0] = 0.f;
+    if (bw[1] != 0.f && (bw[2] != 0.f && bi[2] == bi[1])) bw[1] = 0.f;
+    float ox = 0.f, oy = 0.f, oz = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (bw[k] == 0.f || bi[k] < 0 || bi[k] >= 17) continue;
+      const Xf& T = sFrame[warp][bi[k]];
+      const float wx = px * bw[k], wy = py * bw[k], wz = pz * bw[k], ww = bw[k];
+      ox += T.m[0] * wx + T.m[1] * wy + T.m[2] * wz + T.m[3] * ww;
+      oy += T.m[4] * wx + T.m[5] * wy + T.m[6] * wz + T.m[7] * ww;
+      oz += T.m[8] * wx + T.m[9] * wy + T.m[10] * wz + T.m[11] * ww;
+    }
+    float* o = out + ((size_t)pose * UMT_N_LANDMARKS + lane) * 3;
+    o[0] = ox;
+    o[1] = oy;
+    o[2] = oz;
+  }
 }
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -258,13 +232,8 @@ extern "C" int umt_fk_landmarks(const float* axes, const float* rest, const floa
   if (n == 0) return UMT_OK;
   if (!axes || !rest || !lm_rest || !lm_idx || !lm_w || !joint_angles || !wrist || !out)
     return umt::fail(UMT_ERR_INVALID, "umt_fk_landmarks: null pointer");
-  const int blocks = (n + kFkPoses - 1) / kFkPoses;
-  static bool configured = false;
-  if (!configured) {
-    UMT_CUDA_TRY(cudaFuncSetAttribute(fk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FkShared)));
-    configured = true;
-  }
-  fk_kernel<<<blocks, kFkPoses, sizeof(FkShared), (cudaStream_t)stream>>>(
+  const int blocks = (n + kWarpsPerBlock - 1) / kWarpsPerBlock;
+  fk_kernel<<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(
       axes, rest, lm_rest, lm_idx, lm_w, joint_angles, wrist, mirror, n, out);
   return umt::check_launch("fk_kernel");
 }
