@@ -40,7 +40,9 @@ WANT = ["Kernel Name", "launch__grid_size", "launch__registers_per_thread", "lau
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
         "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
-        "sm__cycles_elapsed.max"]
+        "sm__cycles_elapsed.max", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum"]
 
 
 def full(rep, dst, cmd):
