@@ -439,7 +439,9 @@ def main():
         executed = achieved * (3 if args.mode == "fp32" else 1)
         line["roofline"] = {
             "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-            "frac": achieved / peak_tf, "traffic": ncu_conv_traffic(args.mode),
+            "frac": achieved / peak_tf,
+            "traffic": (ncu_conv_traffic(args.mode) or {}).get("bytes_per_launch"),
+            "traffic_source": ncu_conv_traffic(args.mode),
             "kernel": "conv_umma_kernel (24 launches per encoder pass)",
             "peak_source": peak_src,
             "note": "achieved = algorithmic conv FLOPs / sum of the 24 launch durations (CUDA events inside "

@@ -253,12 +253,9 @@ extern "C" int umt_resample_crops(const uint8_t* src_base, const int64_t* src_of
   if (n_crops == 0) return UMT_OK;
   if (!src_base || !src_offset || !params)
     return umt::fail(UMT_ERR_INVALID, "umt_resample_crops: null input pointer");
-  static bool configured = false;
-  if (!configured) {
-    UMT_CUDA_TRY(cudaFuncSetAttribute(resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      kStageBytes));
-    configured = true;
-  }
+  // per call: the attribute belongs to the current device
+  UMT_CUDA_TRY(cudaFuncSetAttribute(resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    kStageBytes));
   resample_kernel<<<n_crops * 9, kThreads, kStageBytes, (cudaStream_t)stream>>>(
       src_base, src_offset, src_pitch, src_w, src_h, params, out_u8, out_f32, out_idx);
   return umt::check_launch("resample_kernel");
