@@ -191,6 +191,21 @@ def measure_stages(model, hm, hm_dict, dev, peaks):
                                   "hand_frames_per_s": n_hf / dt, "h2d_frame_bytes": frame_bytes,
                                   "note": "raw frames in pinned host memory -> upload + crop cameras + resample + "
                                           "encode + per-frame time scan + FK + metrics, host loop included (best of 3)"}
+    # the reference's own call pattern: one gen_crop_cameras + track_frame per frame (HandTracker)
+    from umetrack_b200.evaluation import track_recording
+    lab1, fr1 = synthetic.make_recording(hm_dict, seed=100, n_frames=48)
+    track_recording(model, lab1, fr1)      # warm-up
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    r1 = track_recording(model, lab1, fr1)
+    torch.cuda.synchronize()
+    dt1 = time.perf_counter() - t0
+    n1 = int(r1["valid_tracking"].sum())
+    out["per_frame_tracker"] = {"frames": 48, "hand_frames": n1, "wall_s": dt1, "ms_per_frame": dt1 / 48 * 1e3,
+                                "hand_frames_per_s": n1 / dt1,
+                                "note": "HandTracker.gen_crop_cameras + track_frame + FK per frame, as "
+                                        "run_eval_known_skeleton.py calls them (host float64 crop cameras, "
+                                        "~41 kernel launches per frame): latency bound"}
     return out
 
 
