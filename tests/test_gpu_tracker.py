@@ -59,3 +59,42 @@ def test_known_skeleton_recording_in_fp16_mode_meets_the_gates():
     d = np.abs(res["tracked_keypoints"] - g["tracked"])[g["valid"]]
     assert d.max() < 0.05, f"fp16 keypoints differ by {d.max()} mm"
     assert abs(res["per_frame_mean_error"].mean() - g["per_frame_error"].mean()) < 0.01
+
+
+def test_device_and_host_crop_cameras_agree():
+    """HandTracker.gen_crop_cameras: the float64 device kernel (default for FishEye62 rigs) against the
+    numpy construction the reference uses -- same hands, same cameras in the same order, parameters
+    equal to float64 round-off (so crop pixel indices cannot differ in practice)."""
+    from umetrack_b200.evaluation import RecordingStream
+    from umetrack_b200.hand_tracker import HandTracker, HandTrackerOpts
+
+    labels, frames = synthetic.make_recording(hm_dict(), seed=3, n_frames=24)
+    tr = HandTracker(UmeTrackModel(synthetic.make_state_dict(0)), HandTrackerOpts())
+    st = RecordingStream(labels, frames)
+    n = 0
+    for frame, gt in st:
+        cams = [v.camera for v in frame.views]
+        tr._device_crop_cameras = True
+        a = tr.gen_crop_cameras(cams, st.camera_angles, st.hand_model, gt, 1)
+        tr._device_crop_cameras = False
+        b = tr.gen_crop_cameras(cams, st.camera_angles, st.hand_model, gt, 1)
+        assert list(a.keys()) == list(b.keys())
+        for h in a:
+            assert list(a[h].keys()) == list(b[h].keys())
+            for c in a[h]:
+                x, y = a[h][c], b[h][c]
+                assert (x.width, x.height) == (y.width, y.height) == (96, 96)
+                np.testing.assert_allclose(np.array(x.f), np.array(y.f), rtol=1e-11)
+                np.testing.assert_allclose(np.array(x.c), np.array(y.c), rtol=1e-11)
+                np.testing.assert_allclose(x.camera_to_world_xf, y.camera_to_world_xf, rtol=0, atol=1e-9)
+                n += 1
+    assert n > 60
+    # min_num_crops = 2 drops single-view hands on both paths alike
+    frame, gt = next(iter(st))
+    cams = [v.camera for v in frame.views]
+    tr._device_crop_cameras = True
+    a = tr.gen_crop_cameras(cams, st.camera_angles, st.hand_model, gt, 2)
+    tr._device_crop_cameras = False
+    b = tr.gen_crop_cameras(cams, st.camera_angles, st.hand_model, gt, 2)
+    assert list(a.keys()) == list(b.keys())
+    assert tr.gen_crop_cameras(cams, st.camera_angles, st.hand_model, {}, 1) == {}

@@ -33,54 +33,75 @@ from .model import InputFrameDesc, InputSkeletonData
 from .skinning import fk_landmarks_device
 
 
-def crop_cameras_device(hand_model: HandModel, labels: dict, device: torch.device,
-                        opts: HandTrackerOpts = HandTrackerOpts(), min_num_crops: int = 1):
-    """Crop cameras for every (frame, hand) of one recording.  Returns a dict of device tensors:
-    sel_count [T,2], sel_cam [T,2,2], resample_params [T,2,2,48] f64, intrinsics [T,2,2,3,3],
-    extrinsics [T,2,2,4,4]; hands with fewer than `min_num_crops` views get sel_count 0."""
-    cams = labels["cameras"]
-    n_cam = len(cams)
-    ja = torch.tensor(np.asarray(labels["joint_angles"]), dtype=torch.float32, device=device)          # [T,2,22]
-    wr = torch.tensor(np.asarray(labels["wrist_transforms"]), dtype=torch.float32, device=device)      # [T,2,4,4]
-    conf = np.asarray(labels["hand_confidences"], dtype=np.float64)                                    # [T,2]
-    T = ja.shape[0]
-    n = T * 2
+def crop_cameras_raw(hand_model: HandModel, ja: torch.Tensor, wr: torch.Tensor, is_right: torch.Tensor,
+                     valid: torch.Tensor, frame_idx: torch.Tensor, intr: torch.Tensor, c2w: torch.Tensor,
+                     angles: torch.Tensor, width: int, height: int,
+                     opts: HandTrackerOpts = HandTrackerOpts()):
+    """umt_crop_cameras for n (frame, hand) items already on the device: ja [n,22] f32, wr [n,4,4] f32
+    (mm), is_right / valid [n] uint8, frame_idx [n] int32 into c2w [T,n_cam,4,4] f64, intr [n_cam,12]
+    f64 (fx fy cx cy k1 k2 k3 k4 p1 p2 k5 k6), angles [n_cam] f64 (degrees).  Returns flat device
+    tensors sel_count [n] i32, sel_cam [n,2] i32, resample_params [n,2,48] f64, intrinsics
+    [n,2,3,3] f32, extrinsics [n,2,4,4] f32 and the error flag [1] i32 (checked by the caller)."""
+    device = ja.device
+    n = ja.shape[0]
+    n_cam = intr.shape[0]
     # three poses per item: given, neutral, open (perspective_crop.py:89-115)
     neutral = neutral_joint_angles(hand_model).to(device=device, dtype=torch.float32)
-    poses = torch.stack([ja.reshape(n, 22), neutral.expand(n, 22), torch.zeros((n, 22), device=device)], dim=1)
+    poses = torch.stack([ja, neutral.expand(n, 22), torch.zeros((n, 22), device=device)], dim=1)
     wrists = wr.reshape(n, 1, 4, 4).expand(n, 3, 4, 4)
-    mirror = torch.tensor([0, 1], dtype=torch.uint8, device=device).repeat(T)                          # hand index
     n_pose = opts.num_crop_points // 21
     pts = fk_landmarks_device(hand_model, poses[:, :n_pose].reshape(-1, 22).contiguous(),
                               wrists[:, :n_pose].reshape(-1, 4, 4).contiguous(),
-                              mirror.repeat_interleave(n_pose)).reshape(n, n_pose * 21, 3).contiguous()
-    valid = torch.from_numpy(((conf > 0) & (conf >= CONFIDENCE_THRESHOLD)).reshape(n).astype(np.uint8)).to(device)
-    frame_idx = torch.arange(T, dtype=torch.int32, device=device).repeat_interleave(2)
-    intr = torch.tensor([[c["fx"], c["fy"], c["cx"], c["cy"]] + [c[k] for k in FISHEYE62_FIELDS] for c in cams],
-                        dtype=torch.float64, device=device)
-    c2w = torch.tensor(np.asarray(labels["camera_to_world_transforms"]), dtype=torch.float64, device=device).contiguous()
-    angles = torch.tensor(labels["camera_angles"], dtype=torch.float64, device=device)
+                              is_right.repeat_interleave(n_pose)).reshape(n, n_pose * 21, 3).contiguous()
     sel_count = torch.zeros(n, dtype=torch.int32, device=device)
     sel_cam = torch.zeros((n, 2), dtype=torch.int32, device=device)
     params = torch.zeros((n, 2, 48), dtype=torch.float64, device=device)
     k_out = torch.zeros((n, 2, 3, 3), dtype=torch.float32, device=device)
     e_out = torch.zeros((n, 2, 4, 4), dtype=torch.float32, device=device)
     err = torch.zeros(1, dtype=torch.int32, device=device)
-    native.check(native.lib().umt_crop_cameras(
-        native.ptr(pts), native.ptr(frame_idx), native.ptr(mirror), native.ptr(valid), native.ptr(intr),
-        native.ptr(c2w), native.ptr(angles), n_cam, int(cams[0]["ImageSizeX"]), int(cams[0]["ImageSizeY"]), n,
-        n_pose * 21, opts.min_required_vis_landmarks, float(opts.hand_ratio_in_crop), native.ptr(sel_count),
-        native.ptr(sel_cam), native.ptr(params), native.ptr(k_out), native.ptr(e_out), native.ptr(err),
-        native.current_stream_ptr()), "umt_crop_cameras")
-    code = int(err.item())
+    with torch.cuda.device(device):
+        native.check(native.lib().umt_crop_cameras(
+            native.ptr(pts), native.ptr(frame_idx), native.ptr(is_right), native.ptr(valid), native.ptr(intr),
+            native.ptr(c2w), native.ptr(angles), n_cam, int(width), int(height), n,
+            n_pose * 21, opts.min_required_vis_landmarks, float(opts.hand_ratio_in_crop), native.ptr(sel_count),
+            native.ptr(sel_cam), native.ptr(params), native.ptr(k_out), native.ptr(e_out), native.ptr(err),
+            native.current_stream_ptr()), "umt_crop_cameras")
+    return {"sel_count": sel_count, "sel_cam": sel_cam, "resample_params": params, "intrinsics": k_out,
+            "extrinsics": e_out, "err": err}
+
+
+def check_crop_camera_error(code: int) -> None:
     if code == 1:
-        raise ValueError("Unable to create crop camera")
+        raise ValueError("Unable to create crop camera")          # lib/common/crop.py:25-26
     if code:
         raise native.NativeError("umt_crop_cameras: singular camera matrix")
-    sel_count = torch.where(sel_count < min_num_crops, torch.zeros_like(sel_count), sel_count)
-    return {"sel_count": sel_count.reshape(T, 2), "sel_cam": sel_cam.reshape(T, 2, 2),
-            "resample_params": params.reshape(T, 2, 2, 48), "intrinsics": k_out.reshape(T, 2, 2, 3, 3),
-            "extrinsics": e_out.reshape(T, 2, 2, 4, 4)}
+
+
+def crop_cameras_device(hand_model: HandModel, labels: dict, device: torch.device,
+                        opts: HandTrackerOpts = HandTrackerOpts(), min_num_crops: int = 1):
+    """Crop cameras for every (frame, hand) of one recording.  Returns a dict of device tensors:
+    sel_count [T,2], sel_cam [T,2,2], resample_params [T,2,2,48] f64, intrinsics [T,2,2,3,3],
+    extrinsics [T,2,2,4,4]; hands with fewer than `min_num_crops` views get sel_count 0."""
+    cams = labels["cameras"]
+    ja = torch.tensor(np.asarray(labels["joint_angles"]), dtype=torch.float32, device=device)          # [T,2,22]
+    wr = torch.tensor(np.asarray(labels["wrist_transforms"]), dtype=torch.float32, device=device)      # [T,2,4,4]
+    conf = np.asarray(labels["hand_confidences"], dtype=np.float64)                                    # [T,2]
+    T = ja.shape[0]
+    n = T * 2
+    mirror = torch.tensor([0, 1], dtype=torch.uint8, device=device).repeat(T)                          # hand index
+    valid = torch.from_numpy(((conf > 0) & (conf >= CONFIDENCE_THRESHOLD)).reshape(n).astype(np.uint8)).to(device)
+    frame_idx = torch.arange(T, dtype=torch.int32, device=device).repeat_interleave(2)
+    intr = torch.tensor([[c["fx"], c["fy"], c["cx"], c["cy"]] + [c[k] for k in FISHEYE62_FIELDS] for c in cams],
+                        dtype=torch.float64, device=device)
+    c2w = torch.tensor(np.asarray(labels["camera_to_world_transforms"]), dtype=torch.float64, device=device).contiguous()
+    angles = torch.tensor(labels["camera_angles"], dtype=torch.float64, device=device)
+    r = crop_cameras_raw(hand_model, ja.reshape(n, 22), wr.reshape(n, 4, 4), mirror, valid, frame_idx, intr, c2w,
+                         angles, int(cams[0]["ImageSizeX"]), int(cams[0]["ImageSizeY"]), opts)
+    check_crop_camera_error(int(r["err"].item()))
+    sel_count = torch.where(r["sel_count"] < min_num_crops, torch.zeros_like(r["sel_count"]), r["sel_count"])
+    return {"sel_count": sel_count.reshape(T, 2), "sel_cam": r["sel_cam"].reshape(T, 2, 2),
+            "resample_params": r["resample_params"].reshape(T, 2, 2, 48),
+            "intrinsics": r["intrinsics"].reshape(T, 2, 2, 3, 3), "extrinsics": r["extrinsics"].reshape(T, 2, 2, 4, 4)}
 
 
 def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]],

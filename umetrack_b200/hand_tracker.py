@@ -166,12 +166,24 @@ class HandTracker:
         self._hand_ratio_in_crop = opts.hand_ratio_in_crop
         self._min_required_vis_landmarks = opts.min_required_vis_landmarks
         self._valid_tracking_history = np.zeros(2, dtype=bool)
+        self._device_crop_cameras = True      # False: always build crop cameras with numpy on the host
+        self._skel_cache = None
+        self._last_hands = None
 
     def reset_history(self) -> None:
         self._valid_tracking_history[:] = False
 
     def gen_crop_cameras(self, cameras, camera_angles, hand_model: HandModel,
                          gt_tracking: Dict[int, SingleHandPose], min_num_crops: int):
+        """Crop cameras of one frame (lib/tracker/tracker.py:101-139).  For the usual rig (FishEye62
+        cameras of one size) all hands go through the float64 device kernel umt_crop_cameras in one
+        launch and one device->host read (it agrees with the numpy construction below to ~1e-13);
+        any other camera model takes the numpy path."""
+        hands = [(h, p) for h, p in (gt_tracking or {}).items() if p.hand_confidence >= CONFIDENCE_THRESHOLD]
+        if hands and self._device_crop_cameras and all(
+                type(c).__name__ == "Fisheye62CameraModel" and c.width == cameras[0].width
+                and c.height == cameras[0].height for c in cameras) and tuple(self._input_size) == (96, 96):
+            return self._gen_crop_cameras_device(cameras, camera_angles, hand_model, hands, min_num_crops)
         out: Dict[int, Dict[int, PinholePlaneCameraModel]] = {}
         for hand_idx, pose in (gt_tracking or {}).items():
             if pose.hand_confidence < CONFIDENCE_THRESHOLD:
@@ -185,13 +197,49 @@ class HandTracker:
                 out[hand_idx] = per_hand
         return out
 
+    def _gen_crop_cameras_device(self, cameras, camera_angles, hand_model: HandModel, hands, min_num_crops: int):
+        from .batched import check_crop_camera_error, crop_cameras_raw
+
+        dev, n, n_cam = self._device, len(hands), len(cameras)
+        # one upload: [intr n_cam*12 | camera_to_world n_cam*16 | angles n_cam | joint angles n*22 | wrists n*16]
+        host = np.concatenate([
+            np.array([[*c.f, *c.c, *c.distort_coeffs] for c in cameras], dtype=np.float64).reshape(-1),
+            np.stack([np.asarray(c.camera_to_world_xf, dtype=np.float64) for c in cameras]).reshape(-1),
+            np.asarray(camera_angles, dtype=np.float64).reshape(-1),
+            np.stack([np.asarray(p.joint_angles, dtype=np.float32) for _, p in hands]).astype(np.float64).reshape(-1),
+            np.stack([np.asarray(p.wrist_xform, dtype=np.float32) for _, p in hands]).astype(np.float64).reshape(-1)])
+        buf = torch.from_numpy(host).to(dev)
+        o = np.cumsum([0, n_cam * 12, n_cam * 16, n_cam, n * 22, n * 16])
+        is_right = torch.tensor([1 if h == RIGHT_HAND_INDEX else 0 for h, _ in hands], dtype=torch.uint8, device=dev)
+        opts = HandTrackerOpts(num_crop_points=self._num_crop_points, hand_ratio_in_crop=self._hand_ratio_in_crop,
+                               min_required_vis_landmarks=self._min_required_vis_landmarks)
+        r = crop_cameras_raw(
+            hand_model, buf[o[3]:o[4]].reshape(n, 22).float(), buf[o[4]:o[5]].reshape(n, 4, 4).float(), is_right,
+            torch.ones(n, dtype=torch.uint8, device=dev), torch.zeros(n, dtype=torch.int32, device=dev),
+            buf[o[0]:o[1]].reshape(n_cam, 12), buf[o[1]:o[2]].reshape(1, n_cam, 4, 4), buf[o[2]:o[3]],
+            cameras[0].width, cameras[0].height, opts)
+        back = torch.cat([r["err"].double(), r["sel_count"].double(), r["sel_cam"].reshape(-1).double(),
+                          r["resample_params"][:, :, 28:48].reshape(-1)]).cpu().numpy()     # one read
+        check_crop_camera_error(int(back[0]))
+        cnt, sel = back[1:1 + n].astype(int), back[1 + n:1 + 3 * n].astype(int).reshape(n, 2)
+        par = back[1 + 3 * n:].reshape(n, 2, 20)
+        out: Dict[int, Dict[int, PinholePlaneCameraModel]] = {}
+        for i, (hand_idx, _) in enumerate(hands):
+            per_hand = {int(sel[i, k]): PinholePlaneCameraModel(
+                width=int(self._input_size[0]), height=int(self._input_size[1]), f=par[i, k, 0:2].copy(),
+                c=par[i, k, 2:4].copy(), distort_coeffs=(), camera_to_world_xf=par[i, k, 4:20].reshape(4, 4).copy())
+                for k in range(int(cnt[i]))}
+            if per_hand and len(per_hand) >= min_num_crops:
+                out[hand_idx] = per_hand
+        return out
+
     def track_frame(self, sample: InputFrame, hand_model: HandModel, crop_cameras) -> TrackingResult:
         if not crop_cameras:
             self.reset_history()
             return TrackingResult()
         data, desc, skel = self._make_inputs(sample, hand_model, crop_cameras)
         out = self._model.regress_pose_use_skeleton(data, desc, skel)
-        return self._gen_tracking_result(out, desc.hand_idx.cpu().numpy(), crop_cameras)
+        return self._gen_tracking_result(out, self._last_hands, crop_cameras)
 
     def track_frame_and_calibrate_scale(self, sample: InputFrame, crop_cameras) -> TrackingResult:
         if not crop_cameras:
@@ -199,7 +247,7 @@ class HandTracker:
             return TrackingResult()
         data, desc, _ = self._make_inputs(sample, None, crop_cameras)
         out = self._model.regress_pose_pred_skel_scale(data, desc)
-        return self._gen_tracking_result(out, desc.hand_idx.cpu().numpy(), crop_cameras)
+        return self._gen_tracking_result(out, self._last_hands, crop_cameras)
 
     def _make_inputs(self, sample: InputFrame, hand_model_mm: Optional[HandModel], crop_cameras):
         pairs, intr, extr, ranges, hands = [], [], [], [], []
@@ -227,16 +275,25 @@ class HandTracker:
             hand_idx=torch.from_numpy(hands_np).long().to(dev))
         skel = None
         if hand_model_mm is not None:
-            hm = scaled_hand_model(hand_model_mm, MM_TO_M)
-            skel = InputSkeletonData(joint_rotation_axes=hm.joint_rotation_axes.float().to(dev),
-                                     joint_rest_positions=hm.joint_rest_positions.float().to(dev))
+            if self._skel_cache is None or self._skel_cache[0] is not hand_model_mm:
+                hm = scaled_hand_model(hand_model_mm, MM_TO_M)     # the same object for a whole recording
+                self._skel_cache = (hand_model_mm, InputSkeletonData(
+                    joint_rotation_axes=hm.joint_rotation_axes.float().to(dev),
+                    joint_rest_positions=hm.joint_rest_positions.float().to(dev)))
+            skel = self._skel_cache[1]
+        self._last_hands = hands_np
         return data, desc, skel
 
     def _gen_tracking_result(self, out: RegressorOutput, hand_indices: np.ndarray, crop_cameras) -> TrackingResult:
-        ja = out.joint_angles.to("cpu").numpy()
-        wr = out.wrist_xfs.to("cpu").numpy()
+        n = out.joint_angles.shape[0]
+        parts = [out.joint_angles.reshape(n, 22), out.wrist_xfs.reshape(n, 16)]
+        if out.skel_scales is not None:
+            parts.append(out.skel_scales.reshape(n, 1))
+        back = torch.cat(parts, dim=1).to("cpu").numpy()            # one device->host read per frame
+        ja = np.ascontiguousarray(back[:, :22])
+        wr = np.ascontiguousarray(back[:, 22:38]).reshape(n, 4, 4)
         wr[..., :3, 3] *= M_TO_MM
-        scales = None if out.skel_scales is None else out.skel_scales.to("cpu").numpy()
+        scales = None if out.skel_scales is None else np.ascontiguousarray(back[:, 38])
         poses, n_views, pred_scales = {}, {}, {}
         for i, h in enumerate(hand_indices):
             h = int(h)
