@@ -206,3 +206,48 @@ def test_torch_data_reader_matches_reference_parser(tmp_path):
         SequenceFolder(str(tmp_path), fields=("x", "a"))                      # 2 items vs 1
     with pytest.raises(TypeError):
         parse_raw_buffers(np.zeros(1), {"unknown_field": [1.0]})
+
+
+def test_torch_idx_round_trip_fuzz(tmp_path):
+    """Property test: whatever write_torch_idx_bin writes, TorchIdx reads back item by item and
+    (for uniform shapes) as one array -- ragged ranks, empty items and every tensor dtype included."""
+    from hypothesis import HealthCheck, given, settings, strategies as st
+
+    from umetrack_b200.torch_data_reader import TorchIdx, write_torch_idx_bin
+
+    dtypes = ["uint8", "int8", "int16", "int32", "int64", "float32", "float64"]
+    shape = st.lists(st.integers(0, 4), min_size=0, max_size=3).map(tuple)
+    counter = [0]
+
+    @settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+    @given(dt=st.sampled_from(dtypes), shapes=st.lists(shape, min_size=1, max_size=5), seed=st.integers(0, 2**31 - 1),
+           uniform=st.booleans())
+    def run(dt, shapes, seed, uniform):
+        if uniform:
+            shapes = [shapes[0]] * len(shapes)
+        rng = np.random.default_rng(seed)
+        items = [(rng.integers(-100, 100, size=s) if "int" in dt else rng.normal(size=s)).astype(dt) for s in shapes]
+        if dt == "uint8":
+            items = [np.abs(a).astype(dt) for a in items]
+        counter[0] += 1
+        p = str(tmp_path / f"f{counter[0]}.torch.idx")
+        write_torch_idx_bin(p, items, dtype=dt)
+        idx = TorchIdx(p)
+        assert len(idx) == len(items) and idx.dtype == np.dtype(dt)
+        for i, a in enumerate(items):
+            got = idx.read_item(i)
+            assert got.shape == a.shape and got.dtype == a.dtype and np.array_equal(got, a)
+        whole = idx.read_bin()
+        if idx.is_uniform:
+            assert np.array_equal(whole, np.stack(items))
+        else:
+            assert all(np.array_equal(w, a) for w, a in zip(whole, items))
+        assert idx.data_size_bytes() == sum(a.nbytes for a in items)
+
+    run()
+    # msgpack items
+    recs = [{"a": [1.5, 2.5], "b": {"c": "x"}}, {}, {"k": list(range(50))}]
+    p = str(tmp_path / "m.torch.idx")
+    write_torch_idx_bin(p, recs)
+    idx = TorchIdx(p)
+    assert idx.is_msgpack and not idx.is_uniform and [idx.read_item(i) for i in range(3)] == recs

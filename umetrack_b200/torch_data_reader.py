@@ -152,7 +152,7 @@ def write_torch_idx_bin(idx_path: str, items: Sequence[Any], dtype: Optional[str
         dims = [(len(b),) for b in blobs]
     else:
         dt = np.dtype(dtype)
-        arrs = [np.ascontiguousarray(it, dtype=dt) for it in items]
+        arrs = [np.asarray(it, dtype=dt, order="C") for it in items]      # (ascontiguousarray would make 0-d items 1-d)
         blobs = [a.tobytes() for a in arrs]
         code, itemsize = _DTYPE_TO_CODE[dt.name], dt.itemsize
         dims = [a.shape for a in arrs]
