@@ -1545,7 +1545,12 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
   // Tuned per output width; override with UMT_CONV_CFG<cout>="S,occ,G,cluster,nbuf" (tools/sweep_conv.py)
   // (B200 sweep, round 1: two co-resident CTAs per SM beat one larger CTA for every width; as many
   // taps per weight stage as shared memory allows)
-  int S = (L.cout == 32) ? 4 : (L.cout == 256 || L.cout % 32 != 0 || L.cout == 96) ? 1 : 2, occ = 2, G = 9, clu = 2, nbuf = 2;
+  // (taps per weight stage: 9 where they fit; 5 / 3 for the 128 / 256-channel layers, whose stages would
+  // otherwise be cut unevenly by the shared-memory budget -- +2 % / +1 %, tools/ab_conv.py)
+  int S = (L.cout == 32) ? 4 : (L.cout == 256 || L.cout % 32 != 0 || L.cout == 96) ? 1 : 2, occ = 2,
+      G = (L.cout == 128) ? 5 : (L.cout == 256) ? 3 : 9, clu = (L.cout == 64 || L.cout == 128) ? 1 : 2, nbuf = 2;
+  // (weight multicast over a CTA pair: neutral for 32 / 256 channels, -1.7 % for 64 / 128 -- the L2 is
+  // not the limit and the cluster hand-shakes cost more than the halved fetch saves)
   int two = 0;
   {
     const std::string name = "UMT_CONV_CFG" + std::to_string(L.cout);
