@@ -223,7 +223,7 @@ __device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) {
 // Issue the MMAs of `n` consecutive taps (one weight stage) for all S sub-tiles.  Descriptors are
 // advanced by adding to their low word: +shift rows for a tap, +128 (2048 B) per sub-tile, +slab
 // bytes per tap on the weight side; everything else is loop invariant.
-template <int S, int COUT, bool SPLIT, bool TWO = false, bool TR = false>
+template <int S, int COUT, bool SPLIT, bool TWO = false>
 __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t0, int n, uint32_t a_lo32,
                                            uint32_t a_hi32, uint32_t a_plane_bytes, uint32_t b_lo32,
                                            uint32_t b_hi32, uint32_t d_base, uint32_t idesc, uint32_t any,
@@ -238,18 +238,6 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
     const uint32_t a0 = a_lo32 + shift16;
     const uint64_t b_hi = desc64(b_lo32 + (uint32_t)j * kBSlab16, b_hi32);
     const uint64_t b_lo = desc64(b_lo32 + (uint32_t)j * kBSlab16 + kBHalf16, b_hi32);
-    if (TR) {
-      // transposed product: the weight slab (M = COUT rows) is the A operand, the S*128 patch rows
-      // starting at this tap's shift are the B operand (N = S*128); one MMA covers every sub-tile
-      const uint64_t x_hi = desc64(a0, a_hi32);
-      tc_mma_bf16<false>(d_base, b_hi, x_hi, idesc, any);
-      if (SPLIT) {
-        if (!skip_hilo) tc_mma_bf16<false>(d_base, b_lo, x_hi, idesc, 1u);
-        tc_mma_bf16<false>(d_base, b_hi, desc64(a0 + a_lo_plane16, a_hi32), idesc, 1u);
-      }
-      any = 1u;
-      continue;
-    }
 #pragma unroll
     for (int s = 0; s < S; ++s) {
       const uint64_t a_hi = desc64(a0 + (uint32_t)s * 128u, a_hi32);
@@ -276,15 +264,10 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
 // warp per scheduler, so every instruction they fetch is on the path that frees the accumulator):
 // 0 = bias/ReLU -> planar rows, 1 = + identity residual, 2 = float32 NCHW output (projection).
 constexpr int kEpiPlain = 0, kEpiResidual = 1, kEpiDense = 2;
-// TR (Cout == 128, S == 2): the product is formed transposed -- D[channel][position] with M = 128
-// channels and N = 256 positions per instruction -- which moves 12 KB of operands per 128 clk of
-// tensor work instead of 16 KB; the epilogue transposes 32x32 blocks back through shared memory.
-constexpr int kTrScratchBytes = 4 * 32 * 32 * 4;   // one 32x32 float block per epilogue warp
-template <int COUT, int MODE, int EPI, bool TR = false>
+template <int COUT, int MODE, int EPI>
 __global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma_kernel(const __grid_constant__ ConvParams P) {
   constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
-  static_assert(!TR || COUT == 128, "transposed form needs M = Cout = 128");
   extern __shared__ __align__(128) uint8_t smem[];
   // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -404,8 +387,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     // ===== MMA issuer: the whole warp walks the program (so every value stays warp-uniform and
     // lives in uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit =====
     constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 7) /* A */ |
-                               ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 10) /* B: 0 = f16, 1 = bf16 */ |
-                               ((uint32_t)((TR ? 256 : COUT) >> 3) << 17) /* N */ | ((128u >> 4) << 24) /* M */;
+                               ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 10) /* B: 0 = f16, 1 = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
+                               ((128u >> 4) << 24);
     const bool leader = elect_one();
     const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
     const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
@@ -445,14 +428,10 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
           const uint32_t b_lo32 = (uint32_t)(b_desc_base & 0xFFFFFFFFu) | ((b_s0 >> 4) & 0x3FFFu);
           const uint32_t b_hi32 = (uint32_t)(b_desc_base >> 32);
           if (leader) {
-            if (TR) {
-              issue_taps<2, COUT, SPLIT, false, true>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo);
-            } else {
-              switch (P.S) {
-                case 1: issue_taps<1, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-                case 2: issue_taps<2, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-                default: issue_taps<4, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-              }
+            switch (P.S) {
+              case 1: issue_taps<1, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              case 2: issue_taps<2, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              default: issue_taps<4, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
             }
             if (cl == 1) tc_commit(b_empty(bslot));
             else tc_commit_multicast(b_empty(bslot), cta_mask);   // frees the slot in every CTA of the cluster
@@ -484,73 +463,6 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
       const int buf = tc % n_buf;
       const long long q0 = (long long)tile * mc;
-      if constexpr (TR) {
-        // ---- transposed accumulator: this warp's lanes are channels 32*lgrp .. +31 (planes
-        // 4*lgrp .. +3), the 256 columns are the tile's positions.  32 columns at a time: bias,
-        // 32x32 transpose through this warp's shared-memory block (16-byte chunks XOR-swizzled by
-        // the row so both the column-wise stores and the row-wise 128-bit loads are conflict
-        // free), then each lane owns one position and writes its four 16-byte rows.
-        float* scr = reinterpret_cast<float*>(smem + P.tr_scratch_off) + (warp - 4) * 1024;
-        const float my_bias = s_bias[lgrp * 32 + lane];
-        const float lo_clamp = P.relu ? 0.0f : -INFINITY;
-        if (EPI == kEpiResidual && q0 + 256 <= P.n_pos) {
-          for (int c0 = 0; c0 < 256; c0 += 32) {
-            const uint8_t* g = P.res.base + (long long)(4 * lgrp) * P.res.plane_stride + (P.res.guard + q0 + c0 + lane) * 16;
-#pragma unroll
-            for (int pl = 0; pl < 4; ++pl) {
-              asm volatile("prefetch.global.L2 [%0];" ::"l"(g + (long long)pl * P.res.plane_stride));
-              if (SPLIT) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + (long long)pl * P.res.plane_stride + P.res.lo_offset));
-            }
-          }
-        }
-        const long long c0w = P.dbg ? clock64() : 0;
-        mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
-        if (P.dbg) w_full += clock64() - c0w;
-        tc_fence_after();
-#pragma unroll 1
-        for (int c0 = 0; c0 < 256; c0 += 32) {
-          uint32_t v[32];
-          const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)buf * buf_cols + (uint32_t)c0;
-          tc_ld16(taddr, v);
-          tc_ld16(taddr + 16, v + 16);
-          const long long q = q0 + c0 + lane;
-          const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
-          uint4 r_h[4], r_l[4];
-          if (EPI == kEpiResidual && o.valid) {
-            const uint8_t* g = P.res.base + (long long)(4 * lgrp) * P.res.plane_stride + (P.res.guard + q) * 16;
-#pragma unroll
-            for (int pl = 0; pl < 4; ++pl) {
-              r_h[pl] = __ldg(reinterpret_cast<const uint4*>(g + (long long)pl * P.res.plane_stride));
-              if (SPLIT) r_l[pl] = __ldg(reinterpret_cast<const uint4*>(g + (long long)pl * P.res.plane_stride + P.res.lo_offset));
-            }
-          }
-          tc_ld_wait();
-          __syncwarp();   // the previous block has been read by every lane
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            scr[i * 32 + ((((lane >> 2) ^ (i & 7)) << 2) | (lane & 3))] = __uint_as_float(v[i]) + my_bias;
-          __syncwarp();
-          if (o.valid) {
-            const FlatTensor& T = P.out[o.tensor];
-#pragma unroll
-            for (int pl = 0; pl < 4; ++pl) {
-              float f[8];
-              const float4 x0 = *reinterpret_cast<const float4*>(scr + lane * 32 + (((2 * pl) ^ (lane & 7)) << 2));
-              const float4 x1 = *reinterpret_cast<const float4*>(scr + lane * 32 + (((2 * pl + 1) ^ (lane & 7)) << 2));
-              f[0] = x0.x; f[1] = x0.y; f[2] = x0.z; f[3] = x0.w; f[4] = x1.x; f[5] = x1.y; f[6] = x1.z; f[7] = x1.w;
-              if (EPI == kEpiResidual) {
-                float r[8];
-                decode_row8<MODE>(r_h[pl], r_l[pl], r);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) f[e] += r[e];
-              }
-#pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], lo_clamp);
-              store_row8<MODE>(T, 4 * lgrp + pl, o.row, f);
-            }
-          }
-        }
-      } else {
       constexpr int kStep = (COUT % 32 == 0) ? 32 : 16;   // columns per TMEM round trip
       constexpr int kRows = kStep / 8;
       // identity residual: the rows of the NEXT chunk are requested before the current chunk is
@@ -636,7 +548,6 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
             }
           }
         }
-      }
       }
       tc_fence_before();
       __syncwarp();
@@ -923,7 +834,7 @@ static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
   size_t bias = ((size_t)cout * 4 + 127) / 128 * 128;
   size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   size_t b = (size_t)2 * (p.two_cta ? cout / 2 : cout) * 16 * (split ? 2 : 1) * p.bgroup;
-  return 1024 + bias + a * p.n_a + b * p.n_b + (p.transposed ? kTrScratchBytes : 0);
+  return 1024 + bias + a * p.n_a + b * p.n_b;
 }
 
 static long long* g_conv_dbg = nullptr;   // set by umt_debug_set_conv_timeline (tools only)
@@ -953,16 +864,7 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   } else if (p.res_epi) {
     kernel = conv_umma_kernel<COUT, MODE, kEpiResidual>;
   }
-  if (p.transposed) {
-    if constexpr (COUT == 128) {
-      if (p.two_cta || p.dense_out || p.S != 2) return fail(UMT_ERR_INVALID, "transposed conv: needs S = 2, one-CTA, planar output");
-      kernel = p.res_epi ? conv_umma_kernel<COUT, MODE, kEpiResidual, true> : conv_umma_kernel<COUT, MODE, kEpiPlain, true>;
-    } else {
-      return fail(UMT_ERR_UNSUPPORTED, "transposed conv only for Cout = 128");
-    }
-  }
   ConvParams pd = p;
-  pd.tr_scratch_off = (int)(smem - kTrScratchBytes);
   pd.dbg = g_conv_dbg;
   UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = std::min(p.n_tiles, sm_count() * std::max(1, p.occ));
@@ -1567,8 +1469,6 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
   p.cluster = std::max(1, std::min(2, clu));
   p.patch_rows = S * 128 + hi - lo;
   p.phase_out = L.phase_out;
-  // Cout = 128: transposed product (see conv_umma_kernel); UMT_CONV_TR=0 keeps the direct form
-  p.transposed = (L.cout == 128 && S == 2 && !p.two_cta && env_int("UMT_CONV_TR", 1)) ? 1 : 0;
   L.n_slabs = (int)(blob.size() / ((size_t)4 * L.cout * 8));
   std::vector<float> bias = main.b;
   if (ds) for (int i = 0; i < L.cout; ++i) bias[i] += ds->b[i];
@@ -1831,15 +1731,10 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
     const bool epi = !p.two_cta && (force >= 0 ? force == 0 : (split || L.cout >= 64));
     if (epi) { p.n_stages -= p.res_stages; p.res_epi = 1; }
   }
-  if (p.transposed && (p.two_cta || p.S != 2)) p.transposed = 0;
-  // measured (B200, round 1): +5 % on layers with the plain epilogue, -2 % with the residual
-  // epilogue (whose transposing version is the longer one); UMT_CONV_TR=2 forces it everywhere
-  if (p.transposed && p.res_epi && env_int("UMT_CONV_TR", 1) < 2) p.transposed = 0;
   // pipeline depths from the shared-memory budget
   const int mc = p.S * 128;
   p.n_tiles = ((p.n_pos + mc - 1) / mc + p.cluster - 1) / p.cluster * p.cluster;
-  const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 108 : 200) * 1024 -
-                        (p.transposed ? kTrScratchBytes : 0);
+  const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 108 : 200) * 1024;
   const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   const size_t fixed = 1024 + ((size_t)L.cout * 4 + 127) / 128 * 128;
   const size_t slab = (size_t)2 * (p.two_cta ? L.cout / 2 : L.cout) * 16 * (split ? 2 : 1);

@@ -57,8 +57,6 @@ struct ConvParams {
   int relu;                 // 1: ReLU in the epilogue
   int res_epi;              // 1: the epilogue adds the identity residual `res` (same raster as the output)
   int res_stages;           // trailing program stages that feed the same residual through identity slabs
-  int transposed;           // 1: D = W (M = 128 channels) x X^T (N = 256 positions), epilogue transposes back
-  int tr_scratch_off;       // byte offset of the epilogue's transpose blocks in dynamic shared memory
   FlatTensor res;
   uint8_t st_src[kMaxStages], st_chunk[kMaxStages], st_ntaps[kMaxStages], st_tap0[kMaxStages];
   uint8_t st_flags[kMaxStages];   // bit 0: weight slab has no lo part (identity slab of a residual)
