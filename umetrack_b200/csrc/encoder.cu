@@ -1734,7 +1734,9 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   // pipeline depths from the shared-memory budget
   const int mc = p.S * 128;
   p.n_tiles = ((p.n_pos + mc - 1) / mc + p.cluster - 1) / p.cluster * p.cluster;
-  const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 108 : 200) * 1024;
+  // 112 KB per CTA: two CTAs plus the per-CTA reserve fill the SM's 228 KB (+4 % on the 256-channel
+  // layers over 108 KB, whose weight stages are the largest; tools/ab_conv.py)
+  const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 112 : 200) * 1024;
   const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   const size_t fixed = 1024 + ((size_t)L.cout * 4 + 127) / 128 * 128;
   const size_t slab = (size_t)2 * (p.two_cta ? L.cout / 2 : L.cout) * 16 * (split ? 2 : 1);
