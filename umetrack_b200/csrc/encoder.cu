@@ -234,7 +234,8 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
   const int tap0 = P.st_tap0[stage] + t0;
 #pragma unroll 1
   for (int j = 0; j < n; ++j) {
-    const uint32_t shift16 = (uint32_t)((int)P.tap_shift[tap0 + j] - P.lo_shift);   // rows == 16-byte units
+    // rows == 16-byte units; merged stages: the tap's patch sits tap_src patches into the plane
+    const uint32_t shift16 = (uint32_t)((int)P.tap_shift[tap0 + j] - P.lo_shift + (int)P.tap_src[tap0 + j] * P.patch_rows);
     const uint32_t a0 = a_lo32 + shift16;
     const uint64_t b_hi = desc64(b_lo32 + (uint32_t)j * kBSlab16, b_hi32);
     const uint64_t b_lo = desc64(b_lo32 + (uint32_t)j * kBSlab16 + kBHalf16, b_hi32);
@@ -275,7 +276,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   float* s_bias = reinterpret_cast<float*>(smem + 1024);
   constexpr int kBiasBytes = ((COUT * 4 + 127) / 128) * 128;
   const int n_a = P.n_a, n_b = P.n_b, n_buf = P.n_buf;
-  const uint32_t a_plane_bytes = (uint32_t)P.patch_rows * 16u;
+  const uint32_t a_patch_bytes = (uint32_t)P.patch_rows * 16u;          // one source's patch in one plane
+  const uint32_t a_plane_bytes = a_patch_bytes * (uint32_t)P.a_nsrc;    // merged stages: a_nsrc patches per plane
   const uint32_t a_stage_bytes = a_plane_bytes * (SPLIT ? 4u : 2u);
   const uint32_t a_stage_stride = (a_stage_bytes + 127u) & ~127u;
   constexpr uint32_t kBHalf = 2u * COUT * 16u;            // one of {w_hi, w_lo}: 2 planes
@@ -338,16 +340,18 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
         mbar_wait(a_empty(slot), ((uint32_t)(it / n_a) & 1u) ^ 1u);
         if (P.dbg) w_aempty += clock64() - c0;
         mbar_expect_tx(a_full(slot), a_stage_bytes);
-        const FlatTensor& T = P.src[P.st_src[i]];
-        const uint8_t* g = T.base + (long long)(2 * P.st_chunk[i]) * T.plane_stride +
-                           ((long long)T.guard + q0 + P.lo_shift) * 16;
-        const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride);
-        bulk_g2s(dst, g, a_plane_bytes, a_full(slot));
-        bulk_g2s(dst + a_plane_bytes, g + T.plane_stride, a_plane_bytes, a_full(slot));
-        if (SPLIT) {
-          bulk_g2s(dst + 2 * a_plane_bytes, g + T.lo_offset, a_plane_bytes, a_full(slot));
-          bulk_g2s(dst + 3 * a_plane_bytes, g + T.lo_offset + T.plane_stride, a_plane_bytes,
-                   a_full(slot));
+        for (int js = 0; js < P.a_nsrc; ++js) {
+          const FlatTensor& T = P.src[P.st_src[i] + js];
+          const uint8_t* g = T.base + (long long)(2 * P.st_chunk[i]) * T.plane_stride +
+                             ((long long)T.guard + q0 + P.lo_shift) * 16;
+          const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride) + (uint32_t)js * a_patch_bytes;
+          bulk_g2s(dst, g, a_patch_bytes, a_full(slot));
+          bulk_g2s(dst + a_plane_bytes, g + T.plane_stride, a_patch_bytes, a_full(slot));
+          if (SPLIT) {
+            bulk_g2s(dst + 2 * a_plane_bytes, g + T.lo_offset, a_patch_bytes, a_full(slot));
+            bulk_g2s(dst + 3 * a_plane_bytes, g + T.lo_offset + T.plane_stride, a_patch_bytes,
+                     a_full(slot));
+          }
         }
       }
     }
@@ -832,7 +836,7 @@ conv_umma2_kernel(const __grid_constant__ ConvParams P) {
 
 static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
   size_t bias = ((size_t)cout * 4 + 127) / 128 * 128;
-  size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
+  size_t a = (((size_t)p.patch_rows * p.a_nsrc * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   size_t b = (size_t)2 * (p.two_cta ? cout / 2 : cout) * 16 * (split ? 2 : 1) * p.bgroup;
   return 1024 + bias + a * p.n_a + b * p.n_b;
 }
@@ -928,8 +932,8 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int mode,
   const int split = (mode == 0);
   const size_t half = (size_t)2 * cout * 16, slab = split ? 2 * half : half;
   for (int i = 0; i < P.n_stages; ++i) {
-    const FlatTensor& T = P.src[P.st_src[i]];
     for (int t = 0; t < P.st_ntaps[i]; ++t, ++k) {
+      const FlatTensor& T = P.src[P.st_src[i] + P.tap_src[P.st_tap0[i] + t]];
       const long long row = q + P.tap_shift[P.st_tap0[i] + t];
       const uint8_t* w = P.weights + (size_t)k * slab;
       for (int pl = 0; pl < 2; ++pl) {
@@ -1355,6 +1359,44 @@ static void pack_identity_slab(std::vector<uint16_t>& blob, int cout, int chunk)
     }
 }
 
+// Stage table of a stride-2 3x3 convolution: tap (ky,kx) reads parity phase ((ky+1)&1, (kx+1)&1) of
+// the input, shifted by -1 row/col iff k == 0.  The four phases contribute 1, 2, 2 and 4 taps; stages
+// that small are dominated by their pipeline hand-shake, so `merge` (1, 2 or 4) consecutive phases share
+// one A stage: their patches sit back to back in each plane and a tap's descriptor shift also selects
+// the patch.  merge = 2 gives stages of 3 and 6 taps, merge = 4 one 9-tap stage per 16 channels (four
+// patches per stage: too much shared memory for the hi/lo split mode).
+static void s2_stage_table(ConvParams& p, int cin, int Wp, int merge, int& ns, int& nt, int& lo, int& hi) {
+  merge = (merge == 4 || merge == 2) ? merge : 1;
+  p.a_nsrc = merge;
+  ns = 0; nt = 0;
+  int tap0[4], cnt[4];
+  for (int ph = 0; ph < 4; ++ph) {
+    tap0[ph] = nt;
+    cnt[ph] = 0;
+    const int py = ph >> 1, px = ph & 1;
+    for (int ky = 0; ky < 3; ++ky) {
+      if (((ky + 1) & 1) != py) continue;
+      for (int kx = 0; kx < 3; ++kx) {
+        if (((kx + 1) & 1) != px) continue;
+        const int shift = (ky == 0 ? -1 : 0) * Wp + (kx == 0 ? -1 : 0);
+        p.tap_src[nt] = (uint8_t)(ph % merge);
+        p.tap_shift[nt++] = (short)shift;
+        lo = std::min(lo, shift);
+        hi = std::max(hi, shift);
+        ++cnt[ph];
+      }
+    }
+  }
+  for (int c = 0; c < cin / 16; ++c)
+    for (int g0 = 0; g0 < 4; g0 += merge) {
+      int n = 0;
+      for (int ph = g0; ph < g0 + merge; ++ph) n += cnt[ph];
+      p.st_src[ns] = (uint8_t)g0; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = (uint8_t)n;
+      p.st_tap0[ns] = (uint8_t)tap0[g0];
+      ++ns;
+    }
+}
+
 // Build program + packed weights of one backbone convolution.
 int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds) {
   ConvParams& p = L.prog;
@@ -1408,36 +1450,21 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
       }
     }
   } else {
-    // stride 2: tap (ky,kx) reads parity phase ((ky+1)&1, (kx+1)&1) shifted by -1 row/col iff k==0
-    int tap0[4];
-    for (int ph = 0; ph < 4; ++ph) {
-      tap0[ph] = nt;
-      const int py = ph >> 1, px = ph & 1;
-      for (int ky = 0; ky < 3; ++ky) {
-        if (((ky + 1) & 1) != py) continue;
-        for (int kx = 0; kx < 3; ++kx) {
-          if (((kx + 1) & 1) != px) continue;
-          add_tap((ky == 0 ? -1 : 0) * Wp + (kx == 0 ? -1 : 0));
-        }
-      }
-    }
+    // stride 2 (see s2_stage_table): weights are packed in phase order, which every grouping shares
+    s2_stage_table(p, main.cin, Wp, env_int("UMT_CONV_S2_MERGE", 2), ns, nt, lo, hi);
     for (int c = 0; c < main.cin / 16; ++c)
       for (int ph = 0; ph < 4; ++ph) {
         const int py = ph >> 1, px = ph & 1;
-        int cnt = 0;
         for (int ky = 0; ky < 3; ++ky) {
           if (((ky + 1) & 1) != py) continue;
           for (int kx = 0; kx < 3; ++kx) {
             if (((kx + 1) & 1) != px) continue;
             pack_slab(blob, main, c, ky, kx);
-            ++cnt;
           }
         }
-        p.st_src[ns] = (uint8_t)ph; p.st_chunk[ns] = (uint8_t)c; p.st_ntaps[ns] = (uint8_t)cnt;
-        p.st_tap0[ns] = (uint8_t)tap0[ph];
-        ++ns;
       }
   }
+  if (p.a_nsrc < 1) p.a_nsrc = 1;
   if (ns > kMaxStages || nt > kMaxTaps) return fail(UMT_ERR_INVALID, "conv program too large");
   p.n_stages = ns;
   p.lo_shift = lo;
@@ -1459,6 +1486,7 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d,%d,%d,%d,%d", &S, &occ, &G, &clu, &nbuf, &two);
   }
   p.two_cta = two ? 1 : 0;
+  if (p.two_cta && p.a_nsrc > 1) return fail(UMT_ERR_INVALID, "two-CTA conv kernel: set UMT_CONV_S2_MERGE=1");
   if (p.two_cta) clu = 2;
   occ = std::max(1, std::min(2, occ));
   while (S > 1 && S * L.cout * occ > 512) S >>= 1;
@@ -1526,6 +1554,14 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     UMT_CUDA_TRY(cudaMalloc(&L.d_weights2_h16, h2.size() * 2));
     m->owned.push_back(L.d_weights2_h16);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights2_h16, h2.data(), h2.size() * 2, cudaMemcpyHostToDevice));
+  }
+  if (main.ks == 3 && L.stride == 2 && !p.two_cta && env_int("UMT_CONV_S2_MERGE", 2) == 2) {
+    // the 16-bit modes have the shared memory for all four phase patches in one stage
+    L.prog16 = p;
+    int ns16 = 0, nt16 = 0, lo16 = 0, hi16 = 0;
+    s2_stage_table(L.prog16, main.cin, Wp, 4, ns16, nt16, lo16, hi16);
+    L.prog16.n_stages = ns16;
+    L.has_prog16 = 1;
   }
   L.d_bias = upload(m, bias);
   if (!L.d_bias) return UMT_ERR_CUDA;
@@ -1694,7 +1730,7 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode);
 
 static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, int mode,
                          ConvParams& p) {
-  p = L.prog;
+  p = (L.has_prog16 && mode != UMT_MODE_FP32_EQUIV) ? L.prog16 : L.prog;
   const int g = L.geom;
   if (L.src_kind == 1) {
     for (int ph = 0; ph < 4; ++ph) p.src[ph] = m->phase[g][ph];
@@ -1737,7 +1773,7 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   // 112 KB per CTA: two CTAs plus the per-CTA reserve fill the SM's 228 KB (+4 % on the 256-channel
   // layers over 108 KB, whose weight stages are the largest; tools/ab_conv.py)
   const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 112 : 200) * 1024;
-  const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
+  const size_t a = (((size_t)p.patch_rows * p.a_nsrc * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   const size_t fixed = 1024 + ((size_t)L.cout * 4 + 127) / 128 * 128;
   const size_t slab = (size_t)2 * (p.two_cta ? L.cout / 2 : L.cout) * 16 * (split ? 2 : 1);
   while (p.bgroup > 1 && fixed + a * 2 + slab * p.bgroup * 3 > budget) --p.bgroup;   // keep >= 3 B stages

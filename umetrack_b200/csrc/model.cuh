@@ -61,6 +61,8 @@ struct ConvParams {
   uint8_t st_src[kMaxStages], st_chunk[kMaxStages], st_ntaps[kMaxStages], st_tap0[kMaxStages];
   uint8_t st_flags[kMaxStages];   // bit 0: weight slab has no lo part (identity slab of a residual)
   short tap_shift[kMaxTaps];
+  uint8_t tap_src[kMaxTaps];   // source of a tap relative to its stage's first source (merged stages)
+  int a_nsrc;                  // consecutive source tensors whose patches share one A stage (1, 2 or 4)
 };
 
 struct ConvLayer {
@@ -79,6 +81,8 @@ struct ConvLayer {
   uint8_t* d_weights2_h16 = nullptr;              // fp16 weights, two-CTA packing
   float* d_bias = nullptr;
   ConvParams prog{};                              // program template (tensors filled per call)
+  ConvParams prog16{};                            // stride-2 layers: stage table used by the 16-bit modes
+  int has_prog16 = 0;
 };
 
 struct Folded {           // conv weight with BatchNorm folded in: w[co][ci][ks*ks], b[co]
