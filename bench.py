@@ -52,7 +52,7 @@ def ncu_conv_traffic(mode):
     """dram__bytes_read + dram__bytes_write per conv_umma_kernel launch, averaged over the 24
     backbone launches of the committed `ncu --set full` capture (fp16 mode, 4096 crops per launch);
     None for the other modes or if the summary is missing.  Bytes per launch, like `achieved`."""
-    path = os.path.join(ROOT, "profiles", "r01_ncu_conv_full_summary_v5.csv")
+    path = os.path.join(ROOT, "profiles", "r01_ncu_conv_full_summary_v6.csv")
     if mode != "fp16" or not os.path.exists(path):
         return None
     import csv
@@ -65,7 +65,7 @@ def ncu_conv_traffic(mode):
             tot += float(r[5]) * 1e9 + float(r[6]) * 1e6   # columns: read [Gbyte], write [Mbyte]
             n += 1
     return {"bytes_per_launch": tot / n, "launches": n, "crops_per_launch": 4096,
-            "source": "profiles/r01_ncu_conv_full_summary_v5.csv"} if n else None
+            "source": "profiles/r01_ncu_conv_full_summary_v6.csv"} if n else None
 
 
 class ClockSampler:
