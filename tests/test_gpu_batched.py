@@ -94,3 +94,25 @@ def test_frame_staging_variants_give_identical_results(tmp_path):
     assert seen == frames.shape[0] and st.bytes_uploaded == frames.size
     with pytest.raises(ValueError):
         list(st.chunks(frames.astype(np.float32)))
+
+
+def test_batched_driver_edge_cases():
+    """Recordings without any trackable hand, a single-frame recording and an empty list."""
+    hm = hm_dict()
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda")
+    lab, fr = synthetic.make_recording(hm, seed=9, n_frames=6)
+    dead = dict(lab)
+    dead["hand_confidences"] = (np.asarray(lab["hand_confidences"]) * 0.0).tolist()
+    one_lab = {k: (v[:1] if k in ("joint_angles", "wrist_transforms", "hand_confidences", "camera_to_world_transforms") else v)
+               for k, v in lab.items()}
+    sums = MetricSums("cuda")
+    res = track_recordings_batched(model, [(dead, fr), (lab, fr), (one_lab, fr[:1])], sums=sums)
+    assert not res[0]["valid_tracking"].any() and res[0]["per_frame_mean_error"].shape == (0,)
+    assert np.all(res[0]["tracked_keypoints"] == 0)
+    ref = track_recordings_batched(model, [(lab, fr)])[0]
+    assert np.array_equal(res[1]["tracked_keypoints"], ref["tracked_keypoints"])      # neighbours do not matter
+    assert res[2]["valid_tracking"].shape == (2, 1)
+    assert np.array_equal(res[2]["tracked_keypoints"][:, 0], ref["tracked_keypoints"][:, 0])   # frame 0: no memory yet
+    r = sums.result()
+    assert r["n_hand_frames"] == float(res[1]["valid_tracking"].sum() + res[2]["valid_tracking"].sum())
+    assert r["n_slots"] == 2 * 6 + 2 * 6 + 2
