@@ -113,6 +113,8 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
     this driver), a tensor already on the device is used in place.  Returns one dict per recording with the arrays the reference pickles
     (tracked_keypoints, gt_keypoints [2,T,21,3] float64 mm, valid_tracking [2,T]) and
     per_frame_mean_error; metric sums are accumulated on the GPU if `sums` is given."""
+    if not recordings:
+        return []
     dev = torch.device("cuda", torch.cuda.current_device())
     model.to(dev)
     model.reset_memory()
