@@ -22,7 +22,7 @@ model.set_mode(mode)
 imgs = torch.rand((n, 96, 96), device="cuda")
 model.encode(imgs)
 names = ["A:wait_empty", "A:total", "B:wait_empty", "M:wait_acc", "M:wait_a", "M:wait_b", "M:total", "M:tiles",
-         "E:wait_full", "E:total", "g0", "g1", "sm", "M:wait_a_peer", "M:wait_b_peer"]
+         "E:wait_full", "E:total", "g0", "g1", "sm"]
 for layer in layers:
     stage = 0 if layer < 4 else 1 if layer < 10 else 2 if layer < 20 else 3
     c, h = {0: (32, 48), 1: (64, 24), 2: (128, 12), 3: (256, 6)}[stage]

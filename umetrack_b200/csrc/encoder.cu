@@ -118,51 +118,14 @@ __device__ __forceinline__ void tc_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                : "memory");
 }
-template <bool TWO = false>
 __device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
                                             uint32_t idesc, uint32_t accumulate) {
-  if (TWO) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-  } else {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-  }
-}
-__device__ __forceinline__ void tc_commit2_multicast(uint32_t bar, uint16_t cta_mask) {
   asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-      ::"r"(bar), "h"(cta_mask)
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
-}
-// arrive on the barrier at the same shared-memory offset in CTA `target_rank` of the cluster
-__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t target_rank) {
-  asm volatile(
-      "{\n\t.reg .b32 ra;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
-      ::"r"(bar), "r"(target_rank)
-      : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t done;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  } while (!done);
 }
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t* v) {
   asm volatile(
@@ -223,12 +186,12 @@ __device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) {
 // Issue the MMAs of `n` consecutive taps (one weight stage) for all S sub-tiles.  Descriptors are
 // advanced by adding to their low word: +shift rows for a tap, +128 (2048 B) per sub-tile, +slab
 // bytes per tap on the weight side; everything else is loop invariant.
-template <int S, int COUT, bool SPLIT, bool TWO = false>
+template <int S, int COUT, bool SPLIT>
 __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t0, int n, uint32_t a_lo32,
                                            uint32_t a_hi32, uint32_t a_plane_bytes, uint32_t b_lo32,
                                            uint32_t b_hi32, uint32_t d_base, uint32_t idesc, uint32_t any,
                                            bool skip_hilo) {
-  constexpr uint32_t kBHalf16 = (2u * (TWO ? COUT / 2 : COUT) * 16u) >> 4;
+  constexpr uint32_t kBHalf16 = (2u * COUT * 16u) >> 4;
   constexpr uint32_t kBSlab16 = SPLIT ? 2u * kBHalf16 : kBHalf16;
   const uint32_t a_lo_plane16 = (2u * a_plane_bytes) >> 4;
   const int tap0 = P.st_tap0[stage] + t0;
@@ -243,11 +206,11 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
     for (int s = 0; s < S; ++s) {
       const uint64_t a_hi = desc64(a0 + (uint32_t)s * 128u, a_hi32);
       const uint32_t d = d_base + (uint32_t)(s * COUT);
-      tc_mma_bf16<TWO>(d, a_hi, b_hi, idesc, any);
+      tc_mma_bf16(d, a_hi, b_hi, idesc, any);
       if (SPLIT) {
         const uint64_t a_lo = desc64(a0 + (uint32_t)s * 128u + a_lo_plane16, a_hi32);
-        if (!skip_hilo) tc_mma_bf16<TWO>(d, a_hi, b_lo, idesc, 1u);
-        tc_mma_bf16<TWO>(d, a_lo, b_hi, idesc, 1u);
+        if (!skip_hilo) tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
+        tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
       }
     }
     any = 1u;
@@ -570,274 +533,10 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   }
 }
 
-// Two-CTA variant (tcgen05 cta_group::2): the CTAs of a cluster pair sit on the two SMs of a TPC;
-// one M=256 MMA, issued by the leader, multiplies 128 positions from EACH CTA's A patch with a
-// weight slab of which each CTA holds only half the output channels.  Per CTA this halves the
-// shared-memory traffic of the weight operand (reads and refills) and the number of MMA
-// instructions.  The peer CTA runs its own producers and epilogue; a relay thread forwards its
-// "stage landed" events to the leader, and the leader's commits are multicast to both CTAs.
-template <int COUT, int MODE>
-__global__ void __launch_bounds__(kConvThreads, 2)
-conv_umma2_kernel(const __grid_constant__ ConvParams P) {
-  constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
-  extern __shared__ __align__(128) uint8_t smem[];
-  // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + 1000);
-  float* s_bias = reinterpret_cast<float*>(smem + 1024);
-  constexpr int kBiasBytes = ((COUT * 4 + 127) / 128) * 128;
-  const int n_a = P.n_a, n_b = P.n_b, n_buf = P.n_buf;
-  const uint32_t a_plane_bytes = (uint32_t)P.patch_rows * 16u;
-  const uint32_t a_stage_bytes = a_plane_bytes * (SPLIT ? 4u : 2u);
-  const uint32_t a_stage_stride = (a_stage_bytes + 127u) & ~127u;
-  constexpr uint32_t kBHalf = 2u * (COUT / 2) * 16u;      // one of {w_hi, w_lo}: 2 planes x Cout/2 rows (this CTA's half of N)
-  constexpr uint32_t kBSlab = SPLIT ? 2u * kBHalf : kBHalf;   // bytes of one (stage, tap) slab in this mode
-  const int G = P.bgroup;                                    // slabs per B pipeline stage
-  const uint32_t b_stage_bytes = (uint32_t)G * kBSlab;
-  uint8_t* a_base = smem + 1024 + kBiasBytes;
-  uint8_t* b_base = a_base + (size_t)n_a * a_stage_stride;
-
-  const uint32_t bar0 = smem_u32(bars);
-  auto a_full = [&](int i) { return bar0 + 8u * (uint32_t)i; };
-  auto a_empty = [&](int i) { return bar0 + 8u * (uint32_t)(n_a + i); };
-  auto b_full = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + i); };
-  auto b_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + n_b + i); };
-  auto acc_full = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + i); };
-  auto acc_empty = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + 2 + i); };
-  // leader only: "the peer CTA's copy of this stage has landed" (one remote arrival per phase)
-  auto a_peer = [&](int i) { return bar0 + 8u * (uint32_t)(2 * n_a + 2 * n_b + 4 + i); };
-  auto b_peer = [&](int i) { return bar0 + 8u * (uint32_t)(3 * n_a + 2 * n_b + 4 + i); };
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint32_t cta_rank = 0;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
-  const bool is_leader = (cta_rank == 0);
-  const uint16_t cta_mask = 3;
-  const int mc = P.S * 128;
-  const uint32_t buf_cols = (uint32_t)(P.S * COUT);
-  const uint32_t want_cols = buf_cols * (uint32_t)n_buf;
-  const uint32_t tmem_cols = want_cols <= 32u ? 32u : want_cols <= 64u ? 64u : want_cols <= 128u ? 128u
-                             : want_cols <= 256u ? 256u : 512u;
-
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < n_a; ++i) { mbar_init(a_full(i), 1); mbar_init(a_empty(i), 1); mbar_init(a_peer(i), 1); }
-    for (int i = 0; i < n_b; ++i) { mbar_init(b_full(i), 1); mbar_init(b_empty(i), 1); mbar_init(b_peer(i), 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(acc_full(i), 1); mbar_init(acc_empty(i), 8); }   // 4 epilogue warps x 2 CTAs
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(tmem_slot)),
-                 "r"(tmem_cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-  }
-  if (warp == 3) {
-    for (int c = lane; c < COUT; c += 32) s_bias[c] = P.bias[c];
-  }
-  tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();   // the peer's barriers must be initialised before any remote arrival
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0 && lane == 0) {
-    // ===== A-patch producer: one 16-channel slice (2 planes hi [+2 planes lo]) per stage =====
-    int it = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      const long long q0 = (long long)tile * mc;
-      for (int i = 0; i < P.n_stages; ++i, ++it) {
-        const int slot = it % n_a;
-        mbar_wait(a_empty(slot), ((uint32_t)(it / n_a) & 1u) ^ 1u);
-        mbar_expect_tx(a_full(slot), a_stage_bytes);
-        const FlatTensor& T = P.src[P.st_src[i]];
-        const uint8_t* g = T.base + (long long)(2 * P.st_chunk[i]) * T.plane_stride +
-                           ((long long)T.guard + q0 + P.lo_shift) * 16;
-        const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride);
-        bulk_g2s(dst, g, a_plane_bytes, a_full(slot));
-        bulk_g2s(dst + a_plane_bytes, g + T.plane_stride, a_plane_bytes, a_full(slot));
-        if (SPLIT) {
-          bulk_g2s(dst + 2 * a_plane_bytes, g + T.lo_offset, a_plane_bytes, a_full(slot));
-          bulk_g2s(dst + 3 * a_plane_bytes, g + T.lo_offset + T.plane_stride, a_plane_bytes,
-                   a_full(slot));
-        }
-      }
-    }
-  } else if (warp == 1 && lane == 0) {
-    // ===== weight-slab producer: one (stage, tap) slab per B stage, multicast over the cluster =====
-    // (up to G consecutive taps of one stage travel as one bulk copy; the packed blob of this
-    // numeric mode is contiguous in program order)
-    int kb = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      int k = 0;
-      for (int i = 0; i < P.n_stages; ++i) {
-        const int nt = P.st_ntaps[i];
-        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
-          const int n = min(G, nt - t0);
-          const int slot = kb % n_b;
-          mbar_wait(b_empty(slot), ((uint32_t)(kb / n_b) & 1u) ^ 1u);
-          const uint32_t bytes = (uint32_t)n * kBSlab;
-          mbar_expect_tx(b_full(slot), bytes);
-          const uint32_t dst = smem_u32(b_base + (size_t)slot * b_stage_bytes);
-          // weights are packed per CTA rank: [rank][slab][hi|lo][2 planes][Cout/2][8]
-          const uint8_t* src = P.weights + (size_t)cta_rank * P.w_rank_stride + (size_t)k * kBSlab;
-          bulk_g2s(dst, src, bytes, b_full(slot));
-          k += n;
-        }
-      }
-    }
-  } else if (warp == 3 && lane == 0 && !is_leader) {
-    // ===== relay (peer CTA only): tell the leader when this CTA's operand stages have landed =====
-    int it = 0, kb = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int i = 0; i < P.n_stages; ++i, ++it) {
-        const int aslot = it % n_a;
-        mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
-        mbar_arrive_remote(a_peer(aslot), 0);
-        const int nt = P.st_ntaps[i];
-        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
-          const int bslot = kb % n_b;
-          mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
-          mbar_arrive_remote(b_peer(bslot), 0);
-        }
-      }
-    }
-  } else if (warp == 2 && is_leader) {
-    // ===== MMA issuer (leader CTA): the whole warp walks the program (so every value stays warp-uniform and
-    // lives in uniform registers); one elected lane issues tcgen05.mma / tcgen05.commit =====
-    constexpr uint32_t idesc = (1u << 4) /* D = f32 */ | ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 7) /* A */ |
-                               ((MODE == UMT_MODE_FP16 ? 0u : 1u) << 10) /* B: 0 = f16, 1 = bf16 */ | ((uint32_t)(COUT >> 3) << 17) |
-                               ((256u >> 4) << 24);   // M = 256: 128 rows from each CTA of the pair
-    const bool leader = elect_one();
-    const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
-    const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
-    const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)((((COUT / 2) * 16u) >> 4) & 0x3FFF) << 16);
-    int it = 0, kb = 0, tc = 0;
-    long long w_acc = 0, w_a = 0, w_b = 0, w_ap = 0, w_bp = 0, t_begin = clock64(), c0 = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
-      const int buf = tc % n_buf;
-      c0 = P.dbg ? clock64() : 0;
-      mbar_wait_cluster(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // both epilogues drained this buffer
-      if (P.dbg) w_acc += clock64() - c0;
-      tc_fence_after();
-      const uint32_t d_base = tmem_base + (uint32_t)buf * buf_cols;
-      uint32_t any = 0;
-      for (int i = 0; i < P.n_stages; ++i, ++it) {
-        const int aslot = it % n_a;
-        c0 = P.dbg ? clock64() : 0;
-        mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
-        if (P.dbg) { w_a += clock64() - c0; c0 = clock64(); }
-        mbar_wait_cluster(a_peer(aslot), (uint32_t)(it / n_a) & 1u);
-        if (P.dbg) w_ap += clock64() - c0;
-        const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
-        const bool skip_hilo = SPLIT && (P.st_flags[i] & 1);   // identity (residual) slabs have w_lo == 0
-        const int nt = P.st_ntaps[i];
-        // low 32 bits of the A descriptors of this stage (start address field, 16-byte units);
-        // tap shift and sub-tile only add to it
-        const uint32_t a_lo32 = (uint32_t)(a_desc_base & 0xFFFFFFFFu) | ((a_s >> 4) & 0x3FFFu);
-        const uint32_t a_hi32 = (uint32_t)(a_desc_base >> 32);
-        for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
-          const int n = min(G, nt - t0);
-          const int bslot = kb % n_b;
-          c0 = P.dbg ? clock64() : 0;
-          mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
-          if (P.dbg) { w_b += clock64() - c0; c0 = clock64(); }
-          mbar_wait_cluster(b_peer(bslot), (uint32_t)(kb / n_b) & 1u);
-          if (P.dbg) w_bp += clock64() - c0;
-          tc_fence_after();
-          const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
-          const uint32_t b_lo32 = (uint32_t)(b_desc_base & 0xFFFFFFFFu) | ((b_s0 >> 4) & 0x3FFFu);
-          const uint32_t b_hi32 = (uint32_t)(b_desc_base >> 32);
-          if (leader) {
-            switch (P.S) {
-              case 1: issue_taps<1, COUT, SPLIT, true>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-              case 2: issue_taps<2, COUT, SPLIT, true>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-              default: issue_taps<4, COUT, SPLIT, true>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-            }
-            tc_commit2_multicast(b_empty(bslot), cta_mask);   // frees the slot in both CTAs
-          }
-          any = 1u;
-          __syncwarp();
-        }
-        if (leader) tc_commit2_multicast(a_empty(aslot), cta_mask);
-        __syncwarp();
-      }
-      if (leader) tc_commit2_multicast(acc_full(buf), cta_mask);
-      __syncwarp();
-    }
-    if (P.dbg && leader) {
-      long long* d = P.dbg + blockIdx.x * 16;
-      d[3] = w_acc; d[4] = w_a; d[5] = w_b; d[6] = clock64() - t_begin; d[7] = tc; d[13] = w_ap; d[14] = w_bp;
-    }
-  } else if (warp >= 4) {
-    // ===== epilogue: TMEM -> registers -> bias / ReLU -> split bf16 -> global =====
-    const int lgrp = warp & 3;  // TMEM lane group this warp may read
-    int tc = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
-      const int buf = tc % n_buf;
-      mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
-      tc_fence_after();
-      const long long q0 = (long long)tile * mc;
-      for (int s = 0; s < P.S; ++s) {
-        const long long q = q0 + s * 128 + lgrp * 32 + lane;
-        const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
-        const FlatTensor& T = P.out[o.tensor];
-        constexpr int kStep = (COUT % 32 == 0) ? 32 : 16;   // columns per TMEM round trip
-        const float lo_clamp = P.relu ? 0.0f : -INFINITY;
-#pragma unroll 1
-        for (int c0 = 0; c0 < COUT; c0 += kStep) {
-          uint32_t v[kStep];
-          const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) +
-                                 (uint32_t)buf * buf_cols + (uint32_t)(s * COUT + c0);
-          tc_ld16(taddr, v);
-          if (kStep == 32) tc_ld16(taddr + 16, v + 16);
-          tc_ld_wait();
-          if (o.valid) {
-#pragma unroll
-            for (int h = 0; h < kStep / 8; ++h) {
-              float f[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e)
-                f[e] = fmaxf(__uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e], lo_clamp);
-              if (P.dense_out) {
-                // float32 NCHW output [n, dense_c, H, W]: lanes hold consecutive pixels, so for each
-                // channel the warp writes (nearly) consecutive floats
-                const long long hw = (long long)P.H * P.W, img = o.dense / hw, pix = o.dense - img * hw;
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                  const int c = c0 + h * 8 + e;
-                  if (c < P.dense_c) P.dense_out[(img * P.dense_c + c) * hw + pix] = f[e];
-                }
-              } else {
-                store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
-              }
-            }
-          }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {   // 8 arrivals (4 epilogue warps x 2 CTAs) on the leader's barrier free the buffer
-        if (is_leader) mbar_arrive(acc_empty(buf));
-        else mbar_arrive_remote(acc_empty(buf), 0);
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();   // nobody leaves while the pair still shares barriers / operands
-  if (warp == 2) {
-    __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                 "r"(tmem_cols)
-                 : "memory");
-  }
-}
-
 static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
   size_t bias = ((size_t)cout * 4 + 127) / 128 * 128;
   size_t a = (((size_t)p.patch_rows * p.a_nsrc * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
-  size_t b = (size_t)2 * (p.two_cta ? cout / 2 : cout) * 16 * (split ? 2 : 1) * p.bgroup;
+  size_t b = (size_t)2 * cout * 16 * (split ? 2 : 1) * p.bgroup;
   return 1024 + bias + a * p.n_a + b * p.n_b;
 }
 
@@ -858,10 +557,7 @@ template <int COUT, int MODE>
 static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   const size_t smem = conv_smem_bytes(p, COUT, MODE == UMT_MODE_FP32_EQUIV);
   void (*kernel)(ConvParams) = conv_umma_kernel<COUT, MODE, kEpiPlain>;
-  if (p.two_cta) {
-    if (p.res_epi) return fail(UMT_ERR_INVALID, "two-CTA conv kernel has no residual epilogue");
-    kernel = conv_umma2_kernel<COUT, MODE>;
-  } else if (p.dense_out) {
+  if (p.dense_out) {
     if constexpr (COUT == 80) kernel = conv_umma_kernel<COUT, MODE, kEpiDense>;
     else return fail(UMT_ERR_UNSUPPORTED, "float32 output epilogue only for the projection width");
     if (p.res_epi) return fail(UMT_ERR_INVALID, "float32 output epilogue has no residual");
@@ -1480,14 +1176,10 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
       G = (L.cout == 128) ? 5 : (L.cout == 256) ? 3 : 9, clu = (L.cout == 64 || L.cout == 128) ? 1 : 2, nbuf = 2;
   // (weight multicast over a CTA pair: neutral for 32 / 256 channels, -1.7 % for 64 / 128 -- the L2 is
   // not the limit and the cluster hand-shakes cost more than the halved fetch saves)
-  int two = 0;
   {
     const std::string name = "UMT_CONV_CFG" + std::to_string(L.cout);
-    if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d,%d,%d,%d,%d", &S, &occ, &G, &clu, &nbuf, &two);
+    if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d,%d,%d,%d", &S, &occ, &G, &clu, &nbuf);
   }
-  p.two_cta = two ? 1 : 0;
-  if (p.two_cta && p.a_nsrc > 1) return fail(UMT_ERR_INVALID, "two-CTA conv kernel: set UMT_CONV_S2_MERGE=1");
-  if (p.two_cta) clu = 2;
   occ = std::max(1, std::min(2, occ));
   while (S > 1 && S * L.cout * occ > 512) S >>= 1;
   p.S = S;
@@ -1512,31 +1204,9 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     m->owned.push_back(L.d_weights_hi);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights_hi, hi.data(), hi.size() * 2, cudaMemcpyHostToDevice));
   }
-  {  // two-CTA packing: each CTA of a pair holds the weight rows of half the output channels
-    const int hc = L.cout / 2;
-    const size_t half = (size_t)2 * L.cout * 8, part = (size_t)2 * hc * 8;   // elements
-    std::vector<uint16_t> w2((size_t)L.n_slabs * 2 * half), w2h((size_t)L.n_slabs * half);
-    for (int r = 0; r < 2; ++r)
-      for (int k = 0; k < L.n_slabs; ++k)
-        for (int hl = 0; hl < 2; ++hl)
-          for (int pl = 0; pl < 2; ++pl)
-            for (int co = 0; co < hc; ++co)
-              for (int e = 0; e < 8; ++e) {
-                const uint16_t v = blob[(size_t)k * 2 * half + (size_t)hl * half + ((size_t)pl * L.cout + r * hc + co) * 8 + e];
-                w2[((size_t)r * L.n_slabs + k) * 2 * part + (size_t)hl * part + ((size_t)pl * hc + co) * 8 + e] = v;
-                if (hl == 0) w2h[((size_t)r * L.n_slabs + k) * part + ((size_t)pl * hc + co) * 8 + e] = v;
-              }
-    UMT_CUDA_TRY(cudaMalloc(&L.d_weights2, w2.size() * 2));
-    m->owned.push_back(L.d_weights2);
-    UMT_CUDA_TRY(cudaMemcpy(L.d_weights2, w2.data(), w2.size() * 2, cudaMemcpyHostToDevice));
-    UMT_CUDA_TRY(cudaMalloc(&L.d_weights2_hi, w2h.size() * 2));
-    m->owned.push_back(L.d_weights2_hi);
-    UMT_CUDA_TRY(cudaMemcpy(L.d_weights2_hi, w2h.data(), w2h.size() * 2, cudaMemcpyHostToDevice));
-  }
-  {  // fp16 weights (UMT_MODE_FP16), both packings.  Values beyond the half range saturate.
-    const int hc = L.cout / 2;
-    const size_t half = (size_t)2 * L.cout * 8, part = (size_t)2 * hc * 8;
-    std::vector<uint16_t> h1((size_t)L.n_slabs * half), h2((size_t)L.n_slabs * half);
+  {  // fp16 weights (UMT_MODE_FP16).  Values beyond the half range saturate.
+    const size_t half = (size_t)2 * L.cout * 8;
+    std::vector<uint16_t> h1((size_t)L.n_slabs * half);
     for (int k = 0; k < L.n_slabs; ++k)
       for (int pl = 0; pl < 2; ++pl)
         for (int co = 0; co < L.cout; ++co)
@@ -1545,17 +1215,12 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
             const float v = bf2f(blob[src]) + bf2f(blob[src + half]);   // hi + lo == the folded fp32 weight (to 2^-17)
             const uint16_t hv = f2h(v);
             h1[(size_t)k * half + ((size_t)pl * L.cout + co) * 8 + e] = hv;
-            const int r = co / hc, cr = co % hc;
-            h2[((size_t)r * L.n_slabs + k) * part + ((size_t)pl * hc + cr) * 8 + e] = hv;
           }
     UMT_CUDA_TRY(cudaMalloc(&L.d_weights_h16, h1.size() * 2));
     m->owned.push_back(L.d_weights_h16);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights_h16, h1.data(), h1.size() * 2, cudaMemcpyHostToDevice));
-    UMT_CUDA_TRY(cudaMalloc(&L.d_weights2_h16, h2.size() * 2));
-    m->owned.push_back(L.d_weights2_h16);
-    UMT_CUDA_TRY(cudaMemcpy(L.d_weights2_h16, h2.data(), h2.size() * 2, cudaMemcpyHostToDevice));
   }
-  if (main.ks == 3 && L.stride == 2 && !p.two_cta && env_int("UMT_CONV_S2_MERGE", 2) == 2) {
+  if (main.ks == 3 && L.stride == 2 && env_int("UMT_CONV_S2_MERGE", 2) == 2) {
     // the 16-bit modes have the shared memory for all four phase patches in one stage
     L.prog16 = p;
     int ns16 = 0, nt16 = 0, lo16 = 0, hi16 = 0;
@@ -1751,20 +1416,14 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, int 
 
 void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   const bool split = (mode == UMT_MODE_FP32_EQUIV);
-  if (p.two_cta) {
-    p.weights = split ? L.d_weights2 : (mode == UMT_MODE_FP16 ? L.d_weights2_h16 : L.d_weights2_hi);
-    p.w_rank_stride = (long long)L.n_slabs * 2 * (L.cout / 2) * 16 * (split ? 2 : 1);
-  } else {
-    p.weights = split ? L.d_weights : (mode == UMT_MODE_FP16 ? L.d_weights_h16 : L.d_weights_hi);
-    p.w_rank_stride = 0;
-  }
+  p.weights = split ? L.d_weights : (mode == UMT_MODE_FP16 ? L.d_weights_h16 : L.d_weights_hi);
   // identity residual: through the epilogue or through identity slabs?  (B200, round 1: the
   // one-MMA identity stages cost a full pipeline hand-shake each, so the epilogue wins wherever
   // it is not itself the bottleneck -- everywhere in the 3-product mode, and for Cout >= 64 in
   // the 16-bit modes.)  UMT_RES_MMA=0/1 forces one way.
   if (p.res_stages > 0) {
     const int force = env_int("UMT_RES_MMA", -1);
-    const bool epi = !p.two_cta && (force >= 0 ? force == 0 : (split || L.cout >= 64));
+    const bool epi = force >= 0 ? force == 0 : (split || L.cout >= 64);
     if (epi) { p.n_stages -= p.res_stages; p.res_epi = 1; }
   }
   // pipeline depths from the shared-memory budget
@@ -1775,7 +1434,7 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   const size_t budget = (size_t)env_int("UMT_CONV_SMEM_KB", L.prog.occ == 2 ? 112 : 200) * 1024;
   const size_t a = (((size_t)p.patch_rows * p.a_nsrc * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   const size_t fixed = 1024 + ((size_t)L.cout * 4 + 127) / 128 * 128;
-  const size_t slab = (size_t)2 * (p.two_cta ? L.cout / 2 : L.cout) * 16 * (split ? 2 : 1);
+  const size_t slab = (size_t)2 * L.cout * 16 * (split ? 2 : 1);
   while (p.bgroup > 1 && fixed + a * 2 + slab * p.bgroup * 3 > budget) --p.bgroup;   // keep >= 3 B stages
   const size_t b = slab * p.bgroup;
   int n_a = env_int("UMT_CONV_NA", 3);

@@ -35,11 +35,9 @@ struct ConvParams {
   FlatTensor src[5];
   FlatTensor out[4];        // [0] for flat output; four parity-phase tensors when phase_out
   const uint8_t* weights;   // packed operand slabs in program order
-  long long w_rank_stride;  // two-CTA packing: bytes between the two CTA ranks' halves
   float* dense_out;         // if set: write float32 NCHW [n, dense_c, H, W] instead of the planar layout
   int dense_c;
   long long* dbg;           // optional [grid][16] cycle counters (tools/conv_timeline.py); nullptr in production
-  int two_cta;              // 1: cta_group::2 kernel (cluster pair shares each MMA)
   const float* bias;        // [COUT]
   int H, W;                 // output-domain geometry
   int n_pos;                // valid positions: n_img * (H+1) * (W+1)
@@ -75,10 +73,7 @@ struct ConvLayer {
   int n_slabs = 0;
   uint8_t* d_weights = nullptr;                   // packed [slab][hi|lo][2][cout][8] bf16
   uint8_t* d_weights_hi = nullptr;                // packed [slab][2][cout][8] bf16 (hi only)
-  uint8_t* d_weights2 = nullptr;                  // two-CTA packing [rank][slab][hi|lo][2][cout/2][8]
-  uint8_t* d_weights2_hi = nullptr;               // two-CTA packing [rank][slab][2][cout/2][8]
   uint8_t* d_weights_h16 = nullptr;               // fp16 weights, one-CTA packing [slab][2][cout][8]
-  uint8_t* d_weights2_h16 = nullptr;              // fp16 weights, two-CTA packing
   float* d_bias = nullptr;
   ConvParams prog{};                              // program template (tensors filled per call)
   ConvParams prog16{};                            // stride-2 layers: stage table used by the 16-bit modes
