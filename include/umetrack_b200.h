@@ -165,6 +165,21 @@ int umt_model_tail(umt_model* m, int head, const float* features, const float* i
                    float* prev_extr, int n_slots, float* out_joint_angles, float* out_wrist,
                    float* out_scale, float* out_sigma, void* stream);
 
+/* umt_model_tail stepped over a whole time scan in one call: the descriptor arrays (sample_range,
+ * memory_idx, use_memory, hand_idx, and the outputs) hold the rows of ALL steps back to back; step s
+ * covers rows [step_first[s], step_first[s] + step_rows[s]) (HOST int arrays; empty steps are skipped)
+ * and runs after step s-1 on the same stream, so the recurrent state carries over exactly as in a
+ * per-frame loop (lib/tracker/tracker.py:141-168 called once per frame).  per_row_skeletons != 0:
+ * skel_axes / skel_rest are [rows,22,3]; else one skeleton [1,22,3] for every row.  Saves the host
+ * round trip per frame: the scan of a recording is launch bound. */
+int umt_model_tail_scan(umt_model* m, int head, const float* features, const float* intrinsics,
+                        const float* extrinsics, const int64_t* sample_range, const int64_t* memory_idx,
+                        const uint8_t* use_memory, const int64_t* hand_idx, int n_img,
+                        const int* step_first, const int* step_rows, int n_steps, const float* skel_axes,
+                        const float* skel_rest, int per_row_skeletons, float* mem_state, float* prev_extr,
+                        int n_slots, float* out_joint_angles, float* out_wrist, float* out_scale,
+                        float* out_sigma, void* stream);
+
 /* Backbone only: images [n_img,96,96] -> features [n_img,72,6,6]
  * (`_image_backbone`, lib/models/model_utils.py:107-138).  Uses the bound workspace. */
 int umt_model_encode(umt_model* m, int mode, const float* images, int n_img, float* features,

@@ -15,6 +15,7 @@ model = UmeTrackModel(synthetic.make_state_dict(0)).to(dev)
 model.set_mode("fp16")
 hm = hm_dict()
 recs = [synthetic.make_recording(hm, seed=100 + r, n_frames=T) for r in range(R)]
+recs = [(lab, torch.from_numpy(fr).pin_memory()) for lab, fr in recs]     # decoded frames in pinned memory, like bench.py
 track_recordings_batched(model, recs[:2])
 torch.cuda.synchronize()
 for _ in range(2):

@@ -293,6 +293,34 @@ extern "C" int umt_model_tail(umt_model* m, int head, const float* features, con
                       out_joint_angles, out_wrist, out_scale, out_sigma, (cudaStream_t)stream);
 }
 
+extern "C" int umt_model_tail_scan(umt_model* m, int head, const float* features, const float* intrinsics,
+                                   const float* extrinsics, const int64_t* sample_range,
+                                   const int64_t* memory_idx, const uint8_t* use_memory,
+                                   const int64_t* hand_idx, int n_img, const int* step_first,
+                                   const int* step_rows, int n_steps, const float* skel_axes,
+                                   const float* skel_rest, int per_row_skeletons, float* mem_state,
+                                   float* prev_extr, int n_slots, float* out_joint_angles, float* out_wrist,
+                                   float* out_scale, float* out_sigma, void* stream) {
+  if (n_steps < 0 || (n_steps > 0 && (!step_first || !step_rows)))
+    return fail(UMT_ERR_INVALID, "umt_model_tail_scan: bad step list");
+  int launches = 0;
+  for (int s = 0; s < n_steps; ++s) {
+    const long long f = step_first[s];
+    const int n = step_rows[s];
+    if (n == 0) continue;
+    if (f < 0 || n < 0) return fail(UMT_ERR_INVALID, "umt_model_tail_scan: step %d = (%lld, %d)", s, f, n);
+    const float* ax = skel_axes ? skel_axes + (per_row_skeletons ? f * 66 : 0) : nullptr;
+    const float* rs = skel_rest ? skel_rest + (per_row_skeletons ? f * 66 : 0) : nullptr;
+    UMT_TRY(umt_model_tail(m, head, features, intrinsics, extrinsics, sample_range + 2 * f, memory_idx + f,
+                           use_memory + f, hand_idx + f, n_img, n, ax, rs, per_row_skeletons ? n : 1, mem_state,
+                           prev_extr, n_slots, out_joint_angles + 22 * f, out_wrist + 16 * f,
+                           out_scale ? out_scale + f : nullptr, out_sigma + 21 * f, stream));
+    launches += m->launches;
+  }
+  if (m) m->launches = launches;
+  return UMT_OK;
+}
+
 extern "C" int umt_model_last_launch_count(const umt_model* m) { return m ? m->launches : 0; }
 
 extern "C" int umt_model_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,

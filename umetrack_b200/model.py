@@ -319,22 +319,16 @@ class UmeTrackModel:
         wr = torch.empty((rows, 4, 4), dtype=torch.float32, device=dev)
         sg = torch.empty((rows, 21), dtype=torch.float32, device=dev)
         lib = native.lib()
-        stream = native.current_stream_ptr()
-        n_img = feats.shape[0]
-        p = {k: t.data_ptr() for k, t in dict(sr=sr, mi=mi, um=um, hi=hi, ax=ax, rs=rs, ja=ja, wr=wr, sg=sg).items()}
-        launches = 0
+        first = (ctypes.c_int * len(step_rows))(*[int(f) for f, _ in step_rows])
+        count = (ctypes.c_int * len(step_rows))(*[int(n) for _, n in step_rows])
         with torch.cuda.device(dev):
-            for first, n in step_rows:
-                if n == 0:
-                    continue
-                native.check(lib.umt_model_tail(
-                    self._handle, native.HEAD_KNOWN, feats.data_ptr(), intr.data_ptr(), extr.data_ptr(),
-                    p["sr"] + first * 16, p["mi"] + first * 8, p["um"] + first, p["hi"] + first * 8, n_img, n,
-                    p["ax"] + first * 264, p["rs"] + first * 264, n, self._mem_features.data_ptr(),
-                    self._prev_extrinsics.data_ptr(), len(self._mem_features), p["ja"] + first * 88,
-                    p["wr"] + first * 64, 0, p["sg"] + first * 84, stream), "umt_model_tail")
-                launches += lib.umt_model_last_launch_count(self._handle)
-        self.last_launch_count = launches
+            native.check(lib.umt_model_tail_scan(
+                self._handle, native.HEAD_KNOWN, feats.data_ptr(), intr.data_ptr(), extr.data_ptr(), sr.data_ptr(),
+                mi.data_ptr(), um.data_ptr(), hi.data_ptr(), feats.shape[0], first, count, len(step_rows),
+                ax.data_ptr(), rs.data_ptr(), 1, self._mem_features.data_ptr(), self._prev_extrinsics.data_ptr(),
+                len(self._mem_features), ja.data_ptr(), wr.data_ptr(), 0, sg.data_ptr(),
+                native.current_stream_ptr()), "umt_model_tail_scan")
+        self.last_launch_count = lib.umt_model_last_launch_count(self._handle)
         return ja, wr, sg
 
     # ---- extras ----------------------------------------------------------------------------

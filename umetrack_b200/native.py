@@ -38,6 +38,8 @@ SIGNATURES = {
                                   c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
     "umt_model_tail": (c_int, [c_void_p, c_int] + [c_void_p] * 7 + [c_int, c_int, c_void_p,
                                c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
+    "umt_model_tail_scan": (c_int, [c_void_p, c_int] + [c_void_p] * 7 + [c_int, c_void_p, c_void_p, c_int,
+                                    c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
     "umt_model_encode": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_encode_static": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_last_launch_count": (c_int, [c_void_p]),
