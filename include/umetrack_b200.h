@@ -202,6 +202,15 @@ int umt_model_encode_static(umt_model* m, int mode, const float* images, int n_i
 /* Number of kernels the last umt_model_forward / umt_model_encode call launched. */
 int umt_model_last_launch_count(const umt_model* m);
 
+/* Sticky status bits that kernels set on the device since the last call of this function; reads
+ * them into *host_status (HOST pointer), clears them, and SYNCHRONISES `stream` (with
+ * umt_model_profile_layers the only entry points that do).  The reference raises a Python exception
+ * (or grows its memory bank, lib/models/temporal.py:101-123) where this library, which never reads
+ * device data on the host, can only record the condition. */
+#define UMT_STATUS_MEMORY_INDEX 1u  /* a memory_idx outside [0, n_slots): that sample ran without memory */
+#define UMT_STATUS_FP16_RANGE 2u    /* UMT_MODE_FP16: an activation left the half range (result has inf) */
+int umt_model_status(umt_model* m, unsigned* host_status, void* stream);
+
 /* Measurement hook: one encoder pass over n_img crops (one chunk) with a CUDA event between
  * consecutive launches; out_ms is a HOST float[26]: stem, the 24 convolutions in execution order,
  * projection.  Synchronises the stream (this is the only entry point that does). */
@@ -215,6 +224,13 @@ int umt_model_profile_layers(umt_model* m, int mode, const float* images, int n_
  * output may be NULL.  out_shape is a HOST int[3] receiving C, H, W. */
 int umt_model_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
                           float* out_simt, float* out_umma, int* out_shape, void* stream);
+
+/* Test hook (allocates and synchronises): the convolution kernels rely on rows of the bound
+ * workspace that are never written and must read as zero -- the halo positions of the padded raster
+ * (which implement the zero padding of backbone_resnet.py:38,49 and separate neighbouring crops), the
+ * guard rows around every plane and the padding beyond the workspace's capacity.  Counts the 16-byte
+ * rows among them that are not zero into *host_nonzero_rows (HOST pointer). */
+int umt_model_debug_halo_check(umt_model* m, long long* host_nonzero_rows, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Stage (c): forward kinematics + skinning, and metric reductions.

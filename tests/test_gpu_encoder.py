@@ -78,3 +78,27 @@ def test_reduced_precision_modes_report_their_error(setup):
         rel[mode] = float((out - feats).abs().max()) / float(feats.abs().max())
     assert 1e-4 < rel["bf16"] < 8e-2, rel   # bf16 really is lower precision, but not garbage
     assert 1e-5 < rel["fp16"] < rel["bf16"] / 3, rel   # 11-bit vs 8-bit significands
+
+
+def test_halo_and_guard_rows_stay_zero_after_ragged_passes(setup):
+    """The zero padding of every 3x3 convolution (lib/models/backbone_resnet.py:38,49) and the
+    separation of neighbouring crops rest on rows of the workspace that no kernel may ever write.
+    After passes at several ragged crop counts, in every numeric mode and over two chunks, all of
+    them must still be zero (there is no compute-sanitizer on this pool to catch a stray store)."""
+    import ctypes
+
+    from umetrack_b200 import native
+    sd, _, imgs, _, feats = setup
+    model = UmeTrackModel(sd, chunk_images=16).to("cuda")
+    big = synthetic.make_model_batch(12, seed=321)["left_images"]        # 24 crops
+    for mode in ("fp32", "bf16", "fp16"):
+        model.set_mode(mode)
+        for n in (24, 16, 9, 1, 23, 5):                                  # 24 and 23 use two passes over the 16-crop chunk
+            model.encode(big[:n])
+    model.set_mode("fp32")
+    out = model.encode(imgs).cpu()                                       # and the results are still right
+    assert float((out - feats).abs().max()) <= 3e-4 * float(feats.abs().max())
+    bad = ctypes.c_longlong(-1)
+    native.check(native.lib().umt_model_debug_halo_check(model._handle, ctypes.byref(bad), native.current_stream_ptr()),
+                 "umt_model_debug_halo_check")
+    assert bad.value == 0, f"{bad.value} halo / guard rows of the activation workspace are no longer zero"

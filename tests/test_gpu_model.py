@@ -127,3 +127,48 @@ def test_sixteen_bit_encoder_mode_meets_the_keypoint_gate(mode, tol_mm):
         kp_ref = _keypoints_mm(hm, ref["joint_angles"], ref["wrist_xfs"])
         worst = max(worst, float((kp - kp_ref).abs().max()))
     assert worst < tol_mm, f"{mode}: keypoints differ from the oracle by {worst} mm"
+
+
+def test_memory_bank_follows_the_index_values_not_the_tensor_identity():
+    """[0] then [1] in a same-sized index tensor (the stale-cache case): the bank must hold both slots
+    and slot 1's memory must be written and used, as the reference's regrowth does
+    (lib/models/temporal.py:101-123).  Checked against the oracle."""
+    sd = synthetic.make_state_dict(0)
+    model = UmeTrackModel(sd).to("cuda")
+    orc = O.OracleModel(sd)
+    hm = hmod.load_hand_model_from_dict(hm_dict())
+    ax, rest = hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None]
+    idx_dev = torch.zeros(1, dtype=torch.int64, device="cuda")       # one tensor, mutated in place
+    for step, (slot, use) in enumerate([(0, False), (0, True), (1, False), (1, True), (0, True)]):
+        b = synthetic.make_model_batch(1, seed=500 + step)
+        b["memory_idx"][:] = slot
+        b["use_memory"][:] = use
+        fd, desc = _inputs(b)
+        idx_dev.fill_(slot)
+        desc.memory_idx = idx_dev
+        out = model.regress_pose_use_skeleton(fd, desc, InputSkeletonData(ax, rest))
+        ref = orc.regress_pose_use_skeleton(b["left_images"], b["intrinsics"], b["extrinsics_xf"], b["sample_range"],
+                                            b["memory_idx"], b["use_memory"], b["hand_idx"], ax, rest)
+        kp = _keypoints_mm(hm, out.joint_angles.cpu(), out.wrist_xfs.cpu())
+        kp_ref = _keypoints_mm(hm, ref["joint_angles"], ref["wrist_xfs"])
+        assert float((kp - kp_ref).abs().max()) < KEYPOINT_TOL_MM, f"step {step}"
+    assert len(model._mem_features) == 2
+    assert float((model._mem_features.cpu() - orc.state.mem).abs().max()) < 5e-4
+    model.check_status()
+
+
+def test_out_of_range_memory_index_is_reported():
+    from umetrack_b200 import native
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda")
+    hm = hmod.load_hand_model_from_dict(hm_dict())
+    skel = InputSkeletonData(hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None])
+    b = synthetic.make_model_batch(2, seed=9)
+    fd, desc = _inputs(b)
+    desc.n_memory_slots = 2
+    model.regress_pose_use_skeleton(fd, desc, skel)
+    model.check_status()                       # indices 0, 1 fit two slots
+    desc.memory_idx = torch.tensor([0, 2], device="cuda")
+    model.regress_pose_use_skeleton(fd, desc, skel)      # broken promise: index 2 with two slots
+    with pytest.raises(native.NativeError, match="memory_idx"):
+        model.check_status()
+    model.check_status()                       # the flag is cleared by the read

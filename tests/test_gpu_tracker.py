@@ -98,3 +98,28 @@ def test_device_and_host_crop_cameras_agree():
     b = tr.gen_crop_cameras(cams, st.camera_angles, st.hand_model, gt, 2)
     assert list(a.keys()) == list(b.keys())
     assert tr.gen_crop_cameras(cams, st.camera_angles, st.hand_model, {}, 1) == {}
+
+
+def test_hand_set_changing_at_equal_size_matches_reference():
+    """Hand 0 alone for three frames, then hand 1 alone, then both: the memory index tensor keeps its
+    size (and, with a caching allocator, its address) while its VALUE changes from [0] to [1].  The
+    reference grows its memory bank when hand 1 first appears alone (lib/models/temporal.py:101-123,
+    lib/tracker/tracker.py:278-285); golden from the unmodified reference
+    (tests/golden/make_recording_golden.py handset)."""
+    import importlib.util
+    import os
+
+    from tests.helpers import GOLDEN
+    spec = importlib.util.spec_from_file_location("make_recording_golden", os.path.join(GOLDEN, "make_recording_golden.py"))
+    mrg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mrg)
+    g = golden("tracker_handset_golden.npz")
+    labels, frames = synthetic.make_recording(hm_dict(), seed=5, n_frames=9, presence=mrg.handset_presence())
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda")
+    res = track_recording(model, labels, frames)
+    assert np.array_equal(res["valid_tracking"], g["valid"]) and g["valid"].sum() == 12
+    d = np.abs(res["tracked_keypoints"] - g["tracked"])[g["valid"]]
+    assert d.max() < 0.05, f"keypoints differ by {d.max()} mm"
+    assert np.abs(res["per_frame_mean_error"] - g["per_frame_error"]).max() < 0.01
+    model.check_status()          # no memory index fell outside the bank
+    assert len(model._mem_features) == 2

@@ -152,3 +152,65 @@ def test_aggregate_metrics_oracle_matches_reference(golden_dir):
     assert f"AUC score: {a['auc']}" in text
     assert f"Mean keypoint accelerations: {a['mean_keypoint_acceleration']}" in text
     assert f"GT mean keypoint accelerations: {a['gt_mean_keypoint_acceleration']}" in text
+
+
+def test_oracle_maps_match_reference_on_every_crop_of_the_256_frame_recording(golden_dir, hand_model_dict):
+    """All 1018 crops of the survey-size recording: the CRC of the oracle's fixed-point map equals the
+    CRC the unmodified reference produced (tests/golden/make_recording_golden.py long), and the
+    sampled uint8 crops are identical in both frame variants."""
+    import importlib.util
+    import zlib
+
+    spec = importlib.util.spec_from_file_location("make_recording_golden", os.path.join(golden_dir, "make_recording_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    g = np.load(os.path.join(golden_dir, "tracker_long_golden.npz"))
+    rows, pick = g["crop_rows"], set(int(i) for i in g["crop_pick"])
+    assert len(rows) == len(g["map_crc"]) == 1018
+    recs = {v: synthetic.make_recording(mg.long_hand_model_dict(hand_model_dict), seed=mg.LONG_SEED, n_frames=mg.LONG_T,
+                                        smooth_images=(v == "smooth")) for v in ("noise", "smooth")}
+    labels = recs["noise"][0]
+    crops = {"noise": [], "smooth": []}
+    for k, row in enumerate(rows):
+        t, c = int(row[0]), int(row[2])
+        cam = labels["cameras"][c]
+        src_xf = np.array(labels["camera_to_world_transforms"][t][c])
+        coeffs = [cam[n] for n in ("k1", "k2", "k3", "k4", "p1", "p2", "k5", "k6")]
+        mx, my = O.warp_map((cam["fx"], cam["fy"]), (cam["cx"], cam["cy"]), coeffs, src_xf, row[3:5], row[5:7],
+                            row[7:].reshape(4, 4))
+        assert mg.map_crc(np.stack([mx, my], axis=-1)) == int(g["map_crc"][k]), f"crop {k}"
+        ix, iy, fx, fy = O.remap_fixed_point_indices(mx, my)
+        s = np.stack([ix * 32 + fx, iy * 32 + fy], axis=-1).astype(np.int32)
+        assert zlib.crc32(np.ascontiguousarray(s).tobytes()) == int(g["map_crc"][k])
+        if k in pick:
+            for v in crops:
+                fr = recs[v][1]
+                src = fr[t].reshape(fr.shape[1], 4, -1)[:, c, :]
+                crops[v].append(O.remap_u8_bilinear(np.ascontiguousarray(src), mx, my))
+    assert np.array_equal(np.stack(crops["noise"]), g["noise_crops_u8"])
+    assert np.array_equal(np.stack(crops["smooth"]), g["smooth_crops_u8"])
+
+
+def test_scaled_and_mirrored_hand_model_match_reference(golden_dir, hand_model_dict):
+    """C4: scaled_hand_model / mirrored_hand_model against the unmodified reference
+    (lib/common/hand.py:65-134), single and batched models.  Host code: runs without a GPU."""
+    from umetrack_b200 import hand_model as hmod
+
+    g = np.load(os.path.join(golden_dir, "hand_model_golden.npz"))
+    hm = hmod.load_hand_model_from_dict(hand_model_dict)
+    batched = type(hm)(*[(v[None].repeat(3, *([1] * v.dim())) if isinstance(v, torch.Tensor) and v.dim() > 0 else v)
+                         for v in hm])
+    s1, s3 = hmod.scaled_hand_model(hm, 1.0375), hmod.scaled_hand_model(batched, 0.91)
+    assert np.array_equal(s1.joint_rest_positions.numpy(), g["s1_rest"])
+    assert np.array_equal(s1.landmark_rest_positions.numpy(), g["s1_lm"])
+    assert np.array_equal(s3.joint_rest_positions.numpy(), g["s3_rest"])
+    assert np.array_equal(s3.landmark_rest_positions.numpy(), g["s3_lm"])
+    assert s1.joint_rotation_axes is hm.joint_rotation_axes
+    m3 = hmod.mirrored_hand_model(batched, torch.tensor([True, False, True]))
+    one = type(hm)(*[(v[None] if isinstance(v, torch.Tensor) and v.dim() > 0 else v) for v in hm])
+    m1 = hmod.mirrored_hand_model(one, torch.tensor([True]))
+    for m, p in ((m3, "m3"), (m1, "m1")):
+        assert np.array_equal(m.joint_rotation_axes.numpy(), g[p + "_axes"])
+        assert np.array_equal(m.joint_rest_positions.numpy(), g[p + "_rest"])
+        assert np.array_equal(m.landmark_rest_positions.numpy(), g[p + "_lm"])
+    assert np.array_equal(batched.joint_rest_positions.numpy()[0], hm.joint_rest_positions.numpy())   # inputs untouched

@@ -48,6 +48,8 @@ def test_static_scratch_encode_matches_workspace_encode_twice():
     rc2, got_second = _encode_static(model, second, out=out_second)    # reuses the array the first call dirtied
     torch.cuda.synchronize()
     assert rc1 == 0 and rc2 == 0, native.lib().umt_last_error()
+    # the launch count of the call is reported on the caller's handle: stem + 24 convolutions + projection
+    assert native.lib().umt_model_last_launch_count(model._handle) == 26
     # neither torch's allocator nor the driver handed out device memory during the two calls
     assert torch.cuda.memory_allocated(dev) == before[0]
     assert torch.cuda.mem_get_info(dev)[0] >= before[1]
@@ -75,3 +77,15 @@ def test_static_scratch_rejects_more_than_its_capacity():
     assert "exceed the static scratch capacity of 4" in msg
     rc0, _ = _encode_static(model, imgs[:0])
     assert rc0 == 0        # empty batch is a no-op
+
+
+def test_static_scratch_rejects_a_call_from_another_device():
+    """The scratch address is resolved for the current device while the weights stay where the model
+    was created; mixing the two must be an argument error, not an illegal address."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    model = UmeTrackModel(synthetic.make_state_dict(0)).to("cuda:0")
+    with torch.cuda.device(1):
+        imgs = torch.zeros((1, 96, 96), dtype=torch.float32, device="cuda:1")
+        rc, _ = _encode_static(model, imgs)
+    assert rc == 1 and "lives on device 0" in native.lib().umt_last_error().decode()

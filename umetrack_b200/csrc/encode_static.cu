@@ -80,21 +80,33 @@ extern "C" int umt_model_encode_static(umt_model* m, int mode, const float* imag
     return umt::fail(UMT_ERR_INVALID,
                      "umt_model_encode_static: %d crops exceed the static scratch capacity of %d crops; "
                      "use umt_model_encode with a bound workspace for larger batches", n_img, kStaticMaxCrops);
+  // The weights live on one device; the scratch address below is resolved for the CURRENT device.
+  // A mismatch would hand kernels pointers of two different devices.
+  UMT_TRY(umt::check_device(m, "umt_model_encode_static"));
   uint8_t* scratch = nullptr;
   UMT_TRY(static_scratch_for_current_device(&scratch));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // The array keeps the previous call's activations; halo and guard rows must read as zero.
   UMT_CUDA_TRY(cudaMemsetAsync(scratch, 0, umt::encoder_workspace_bytes(kStaticMaxCrops), st));
-  // A private view of the model whose activation tensors live in the static array.  The caller's
-  // handle (and any workspace bound to it) is left untouched.
-  umt_model view;
-  view.convs = m->convs;      // layer programs + device weight pointers (host-side copy only)
-  view.tw = m->tw;
-  view.proj_conv = m->proj_conv;
-  view.chunk_images = kStaticMaxCrops;
-  view.ws = scratch;
-  view.ws_bytes = kStaticScratchBytes;
-  view.ws_max_images = kStaticMaxCrops;
-  umt::encoder_bind(&view, scratch);
-  return umt::encoder_run_chunk(&view, mode, images, n_img, features, -1, st, nullptr);
+  // A private view of the model whose activation tensors live in the static array; the caller's
+  // handle (and any workspace bound to it) is left untouched.  The view is a host object built on
+  // the first call and kept with the model: layer programs + device weight pointers, no device memory.
+  if (!m->static_view) {
+    umt_model* view = new umt_model();
+    view->convs = m->convs;
+    view->tw = m->tw;
+    view->proj_conv = m->proj_conv;
+    view->device = m->device;
+    view->d_status = m->d_status;
+    view->chunk_images = kStaticMaxCrops;
+    view->ws = scratch;
+    view->ws_bytes = kStaticScratchBytes;
+    view->ws_max_images = kStaticMaxCrops;
+    umt::encoder_bind(view, scratch);
+    m->static_view = view;
+  }
+  m->static_view->launches = 0;
+  const int rc = umt::encoder_run_chunk(m->static_view, mode, images, n_img, features, -1, st, nullptr);
+  m->launches = m->static_view->launches;   // umt_model_last_launch_count(m) reports this call
+  return rc;
 }

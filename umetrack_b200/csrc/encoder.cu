@@ -1511,6 +1511,51 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
   return UMT_OK;
 }
 
+// Test hook: count the 16-byte rows that must always read as zero but do not -- guard rows before
+// position 0 and after the padded end of every plane, the halo positions (x == W or y == H) of every
+// image the workspace can hold, and the padding positions beyond its capacity.
+__global__ void halo_check_kernel(FlatTensor T, int planes, int H, int n_cap, unsigned long long* count) {
+  const long long rows = T.plane_stride / 16;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rows * planes) return;
+  const int pl = (int)(idx / rows);
+  const long long r = idx - (long long)pl * rows, q = r - T.guard;
+  const int Wp = H + 1, S = Wp * Wp;
+  bool must_be_zero = q < 0 || q >= (long long)n_cap * S;
+  if (!must_be_zero) {
+    const int rem = (int)(q % S), y = rem / Wp, x = rem - y * Wp;
+    must_be_zero = (x == H) || (y == H);
+  }
+  if (!must_be_zero) return;
+  // planes [0, planes/2) are the hi planes, the rest the lo planes (lo_offset = plane_stride * C/8)
+  const uint4 v = *reinterpret_cast<const uint4*>(T.base + (long long)pl * T.plane_stride + r * 16);
+  if (v.x | v.y | v.z | v.w) atomicAdd(count, 1ull);
+}
+
+int encoder_halo_check(umt_model* m, long long* host_nonzero, cudaStream_t st) {
+  if (!m->ws) return fail(UMT_ERR_INVALID, "no workspace bound");
+  unsigned long long* d = nullptr;
+  UMT_CUDA_TRY(cudaMalloc(&d, sizeof(*d)));          // test hook: may allocate
+  cudaMemsetAsync(d, 0, sizeof(*d), st);
+  auto run = [&](const FlatTensor& T, int C, int H) {
+    const int planes = 2 * (C / 8);
+    const long long total = T.plane_stride / 16 * planes;
+    halo_check_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(T, planes, H, m->chunk_images, d);
+  };
+  for (int g = 0; g < 4; ++g) {
+    for (int b = 0; b < 3; ++b) run(m->buf[g][b], kStageC[g], kStageHW[g]);
+    if (g > 0)
+      for (int ph = 0; ph < 4; ++ph) run(m->phase[g][ph], kStageC[g - 1], kStageHW[g]);
+  }
+  unsigned long long h = 0;
+  cudaError_t e = cudaMemcpyAsync(&h, d, sizeof(h), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(UMT_ERR_CUDA, "halo check: %s", cudaGetErrorString(e));
+  *host_nonzero = (long long)h;
+  return UMT_OK;
+}
+
 int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
                         float* out_simt, float* out_umma, int* shape, cudaStream_t st) {
   if (layer < 0 || layer >= (int)m->convs.size()) return fail(UMT_ERR_INVALID, "layer %d out of range", layer);

@@ -108,6 +108,14 @@ float* upload(umt_model* m, const std::vector<float>& v) {
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+int check_device(const umt_model* m, const char* what) {
+  int dev = -1;
+  UMT_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev != m->device)
+    return fail(UMT_ERR_INVALID, "%s: the model lives on device %d but device %d is current", what, m->device, dev);
+  return UMT_OK;
+}
+
 }  // namespace umt
 
 using namespace umt;
@@ -139,6 +147,12 @@ extern "C" int umt_model_create(const float* const* host_tensors, int n_tensors,
   if (major != 10)
     return fail(UMT_ERR_UNSUPPORTED, "umetrack_b200 needs an sm_100 GPU (tcgen05); device %d is sm_%d", dev, major * 10);
   umt_model* m = new umt_model();
+  m->device = dev;
+  if (cudaMalloc(&m->d_status, sizeof(unsigned)) != cudaSuccess || cudaMemset(m->d_status, 0, sizeof(unsigned)) != cudaSuccess) {
+    delete m;
+    return fail(UMT_ERR_CUDA, "umt_model_create: status word allocation failed");
+  }
+  m->owned.push_back(m->d_status);
   int rc = encoder_build(m, host_tensors);
   if (rc == UMT_OK) rc = tail_build(m, host_tensors);
   if (rc != UMT_OK) {
@@ -152,6 +166,7 @@ extern "C" int umt_model_create(const float* const* host_tensors, int n_tensors,
 extern "C" void umt_model_destroy(umt_model* m) {
   if (!m) return;
   for (void* p : m->owned) cudaFree(p);
+  delete m->static_view;   // host object only: it borrows the weights and owns no device memory
   delete m;
 }
 
@@ -219,6 +234,7 @@ extern "C" int umt_model_encode(umt_model* m, int mode, const float* images, int
   if (!m || !images || !features) return fail(UMT_ERR_INVALID, "umt_model_encode: null argument");
   if (mode < UMT_MODE_FP32_EQUIV || mode > UMT_MODE_FP16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_encode: no workspace bound");
+  UMT_TRY(check_device(m, "umt_model_encode"));
   if (n_img < 0) return fail(UMT_ERR_INVALID, "umt_model_encode: n_img=%d", n_img);
   m->launches = 0;
   if (n_img == 0) return UMT_OK;
@@ -238,6 +254,7 @@ extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* 
   if (head != UMT_HEAD_KNOWN_SKELETON && head != UMT_HEAD_UNKNOWN_SKELETON)
     return fail(UMT_ERR_INVALID, "bad head %d", head);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_forward: no workspace bound");
+  UMT_TRY(check_device(m, "umt_model_forward"));
   if (n_img <= 0 || n_samples <= 0 || n_img > m->ws_max_images || n_samples > m->ws_max_samples)
     return fail(UMT_ERR_INVALID, "umt_model_forward: n_img=%d n_samples=%d exceed the bound workspace (%d, %d)",
                 n_img, n_samples, m->ws_max_images, m->ws_max_samples);
@@ -274,6 +291,7 @@ extern "C" int umt_model_tail(umt_model* m, int head, const float* features, con
   if (head != UMT_HEAD_KNOWN_SKELETON && head != UMT_HEAD_UNKNOWN_SKELETON)
     return fail(UMT_ERR_INVALID, "bad head %d", head);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_tail: no workspace bound");
+  UMT_TRY(check_device(m, "umt_model_tail"));
   if (n_img <= 0 || n_samples <= 0 || n_samples > m->ws_max_samples)
     return fail(UMT_ERR_INVALID, "umt_model_tail: n_samples=%d exceeds the bound workspace (%d)", n_samples,
                 m->ws_max_samples);
@@ -323,12 +341,28 @@ extern "C" int umt_model_tail_scan(umt_model* m, int head, const float* features
 
 extern "C" int umt_model_last_launch_count(const umt_model* m) { return m ? m->launches : 0; }
 
+extern "C" int umt_model_status(umt_model* m, unsigned* host_status, void* stream) {
+  if (!m || !host_status) return fail(UMT_ERR_INVALID, "umt_model_status: null argument");
+  UMT_TRY(check_device(m, "umt_model_status"));
+  cudaStream_t st = (cudaStream_t)stream;
+  UMT_CUDA_TRY(cudaMemcpyAsync(host_status, m->d_status, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+  UMT_CUDA_TRY(cudaMemsetAsync(m->d_status, 0, sizeof(unsigned), st));
+  UMT_CUDA_TRY(cudaStreamSynchronize(st));
+  return UMT_OK;
+}
+
 extern "C" int umt_model_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
                                      float* out_simt, float* out_umma, int* out_shape, void* stream) {
   if (!m || !images) return fail(UMT_ERR_INVALID, "umt_model_debug_layer: null argument");
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_debug_layer: no workspace bound");
   return encoder_debug_layer(m, mode, layer, images, n_img, out_simt, out_umma, out_shape,
                              (cudaStream_t)stream);
+}
+
+extern "C" int umt_model_debug_halo_check(umt_model* m, long long* host_nonzero_rows, void* stream) {
+  if (!m || !host_nonzero_rows) return fail(UMT_ERR_INVALID, "umt_model_debug_halo_check: null argument");
+  UMT_TRY(check_device(m, "umt_model_debug_halo_check"));
+  return encoder_halo_check(m, host_nonzero_rows, (cudaStream_t)stream);
 }
 
 extern "C" int umt_model_profile_layers(umt_model* m, int mode, const float* images, int n_img,

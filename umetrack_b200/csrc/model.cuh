@@ -113,6 +113,9 @@ struct umt_model {
   std::vector<umt::ConvLayer> tail_convs; // fusion(3), temporal(3), regressor_k(4), regressor_u(4)
   umt::FlatTensor tail_flat[3]{};         // 6x6 planar flat scratch, 144 channels capacity
   int launches = 0;
+  int device = -1;                        // device the weights were uploaded to (umt_model_create)
+  unsigned* d_status = nullptr;           // sticky UMT_STATUS_* bits set by kernels, read by umt_model_status
+  umt_model* static_view = nullptr;       // host-side view used by umt_model_encode_static (no device memory)
 };
 
 namespace umt {
@@ -122,6 +125,7 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
                       int stop_after_layer, cudaStream_t st, cudaEvent_t* ev = nullptr);
 int encoder_debug_layer(umt_model* m, int mode, int layer, const float* images, int n_img,
                         float* out_simt, float* out_umma, int* shape, cudaStream_t st);
+int encoder_halo_check(umt_model* m, long long* host_nonzero, cudaStream_t st);
 size_t encoder_workspace_bytes(int chunk_images);
 void encoder_bind(umt_model* m, uint8_t* base);
 void set_conv_debug_buffer(long long* p);
@@ -139,6 +143,7 @@ int tail_forward(umt_model* m, int head, const float* feats, const float* intrin
                  float* prev_extr, int n_slots, float* out_joint_angles, float* out_wrist,
                  float* out_scale, float* out_sigma, cudaStream_t st);
 // model.cu
+int check_device(const umt_model* m, const char* what);   // current device must be the model's
 int tensor_index(const char* name);   // index into the umt_model_create tensor list, -1 if absent
 float* upload(umt_model* m, const std::vector<float>& v);
 }  // namespace umt

@@ -171,7 +171,8 @@ temporal_prepare_kernel(FlatTensor fused_raw /* 80 ch, 72 valid */, const float*
                         const float* __restrict__ intrinsics, const float* __restrict__ extrinsics,
                         const int64_t* __restrict__ sample_range, const int64_t* __restrict__ memory_idx,
                         const uint8_t* __restrict__ use_memory, float* __restrict__ mem_state,
-                        float* __restrict__ prev_extr, int n_slots, FlatTensor tin /* 96 ch */) {
+                        float* __restrict__ prev_extr, int n_slots, FlatTensor tin /* 96 ch */,
+                        unsigned* __restrict__ status) {
   __shared__ float sS[12];
   __shared__ float sM[12];
   __shared__ int sUse;
@@ -182,6 +183,9 @@ temporal_prepare_kernel(FlatTensor fused_raw /* 80 ch, 72 valid */, const float*
   const int slot = (int)memory_idx[b];
   const bool slot_ok = slot >= 0 && slot < n_slots;
   if (threadIdx.x == 0) {
+    // a memory index outside the bank runs without memory (the reference would have grown the bank,
+    // temporal.py:101-123): report it instead of hiding it
+    if (!slot_ok) atomicOr(status, (unsigned)UMT_STATUS_MEMORY_INDEX);
     for (int i = 0; i < 12; ++i) sS[i] = 0.f;
     sS[0] = sS[5] = 1.f;
     sS[10] = intrinsics[(size_t)r0 * 9] / 200.0f;
@@ -580,7 +584,7 @@ int tail_forward(umt_model* m, int head, const float* feats, const float* intrin
   UMT_TRY(run_tail_conv(m, 1, T1, T2, nullptr, B, st));
   UMT_TRY(run_tail_conv(m, 2, T2, T0, nullptr, B, st));
   temporal_prepare_kernel<<<B, 128, 0, st>>>(T0, feats, intrinsics, extrinsics, sample_range, memory_idx,
-                                             use_memory, mem_state, prev_extr, n_slots, T1);
+                                             use_memory, mem_state, prev_extr, n_slots, T1, m->d_status);
   UMT_TRY(check_launch("temporal_prepare_kernel"));
   UMT_TRY(run_tail_conv(m, 3, T1, T2, nullptr, B, st));
   UMT_TRY(run_tail_conv(m, 4, T2, T0, nullptr, B, st));

@@ -56,20 +56,23 @@ class RecordingStream:
 
 
 def track_recording(model, labels: dict, frames: np.ndarray, hand_model: Optional[HandModel] = None,
-                    sums: Optional[MetricSums] = None):
+                    sums: Optional[MetricSums] = None, tracker: Optional[HandTracker] = None):
     """Known-skeleton tracking of one recording.  Returns dict with tracked_keypoints,
     gt_keypoints [2,T,21,3] (float64, mm), valid_tracking [2,T] and per_frame_mean_error --
-    the same arrays the reference pickles (run_eval_known_skeleton.py:92-100)."""
+    the same arrays the reference pickles (run_eval_known_skeleton.py:92-100).  `hand_model`
+    replaces the recording's own model for the PREDICTED keypoints only (the calibrated model of
+    run_eval_unknown_skeleton.py:119-127); crop cameras and ground-truth keypoints always use the
+    recording's model.  `tracker` continues an existing tracker (pass 2 after calibration)."""
     stream = RecordingStream(labels, frames)
     T = len(stream)
     pred_model = stream.hand_model if hand_model is None else hand_model
     tracked = np.zeros([NUM_HANDS, T, NUM_LANDMARKS_PER_HAND, 3])
     gtk = np.zeros([NUM_HANDS, T, NUM_LANDMARKS_PER_HAND, 3])
     valid = np.zeros([NUM_HANDS, T], dtype=bool)
-    tracker = HandTracker(model, HandTrackerOpts())
+    tracker = tracker or HandTracker(model, HandTrackerOpts())
     for t, (frame, gt) in enumerate(stream):
         cc = tracker.gen_crop_cameras([v.camera for v in frame.views], stream.camera_angles,
-                                      pred_model, gt, min_num_crops=1)
+                                      stream.hand_model, gt, min_num_crops=1)
         res = tracker.track_frame(frame, pred_model, cc)
         hands = sorted(res.hand_poses.keys())
         if not hands:
@@ -95,19 +98,36 @@ def track_recording(model, labels: dict, frames: np.ndarray, hand_model: Optiona
 
 
 def calibrate_scale(model, labels: dict, frames: np.ndarray, generic_hand_model: HandModel,
-                    n_calibration_samples: int = 30):
-    """Pass 1 of the unknown-skeleton eval: mean predicted scale over the first
-    `n_calibration_samples` two-view hand-frames -> scaled generic hand model."""
+                    n_calibration_samples: int = 30, tracker: Optional[HandTracker] = None):
+    """Pass 1 of the unknown-skeleton eval (run_eval_unknown_skeleton.py:49-78): mean predicted scale
+    over the first `n_calibration_samples` two-view hand-frames (0 = all) -> scaled generic hand
+    model.  Crop cameras come from the recording's own hand model, like the reference's."""
     stream = RecordingStream(labels, frames)
-    tracker = HandTracker(model, HandTrackerOpts())
+    tracker = tracker or HandTracker(model, HandTrackerOpts())
     scales = []
     for frame, gt in stream:
         cc = tracker.gen_crop_cameras([v.camera for v in frame.views], stream.camera_angles,
-                                      generic_hand_model, gt, min_num_crops=2)
+                                      stream.hand_model, gt, min_num_crops=2)
         res = tracker.track_frame_and_calibrate_scale(frame, cc)
         for h in res.hand_poses.keys():
             scales.append(res.predicted_scales[h])
-        if len(scales) >= n_calibration_samples:
+        if n_calibration_samples != 0 and len(scales) >= n_calibration_samples:
+            scales = scales[:n_calibration_samples]
             break
-    mean_scale = float(np.mean(scales)) if scales else 1.0
+    assert len(scales) > 0, "No samples collected for scale calibration!"
+    mean_scale = float(np.mean(scales))
     return scaled_hand_model(generic_hand_model, mean_scale), mean_scale, np.array(scales)
+
+
+def track_recording_unknown_skeleton(model, labels: dict, frames: np.ndarray, generic_hand_model: HandModel,
+                                     n_calibration_samples: int = 30, sums: Optional[MetricSums] = None):
+    """The whole unknown-skeleton eval of one recording (run_eval_unknown_skeleton.py:82-131):
+    calibration pass, history reset (the recurrent memory is not cleared: it is zeroed lazily by
+    use_memory=False on the next frame), then the known-skeleton loop with the calibrated model for
+    the predictions.  Returns (result dict of track_recording, mean_scale, scales)."""
+    tracker = HandTracker(model, HandTrackerOpts())
+    calibrated, mean_scale, scales = calibrate_scale(model, labels, frames, generic_hand_model,
+                                                     n_calibration_samples, tracker=tracker)
+    tracker.reset_history()
+    res = track_recording(model, labels, frames, hand_model=calibrated, sums=sums, tracker=tracker)
+    return res, mean_scale, scales

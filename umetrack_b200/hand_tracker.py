@@ -172,6 +172,7 @@ class HandTracker:
 
     def reset_history(self) -> None:
         self._valid_tracking_history[:] = False
+        self._skel_cache = None
 
     def gen_crop_cameras(self, cameras, camera_angles, hand_model: HandModel,
                          gt_tracking: Dict[int, SingleHandPose], min_num_crops: int):
@@ -272,12 +273,16 @@ class HandTracker:
             sample_range=torch.tensor(ranges, dtype=torch.int64, device=dev),
             memory_idx=torch.from_numpy(hands_np).long().to(dev),
             use_memory=torch.from_numpy(self._valid_tracking_history[hands_np]).bool().to(dev),
-            hand_idx=torch.from_numpy(hands_np).long().to(dev))
+            hand_idx=torch.from_numpy(hands_np).long().to(dev),
+            n_memory_slots=NUM_HANDS)        # memory_idx is a hand index: the bank always has both slots
         skel = None
         if hand_model_mm is not None:
-            if self._skel_cache is None or self._skel_cache[0] is not hand_model_mm:
-                hm = scaled_hand_model(hand_model_mm, MM_TO_M)     # the same object for a whole recording
-                self._skel_cache = (hand_model_mm, InputSkeletonData(
+            # the metre-scaled skeleton is rebuilt when the hand model's tensors change (also in place)
+            key = tuple((t.data_ptr(), t._version) for t in (hand_model_mm.joint_rotation_axes,
+                                                            hand_model_mm.joint_rest_positions))
+            if self._skel_cache is None or self._skel_cache[0] != key:
+                hm = scaled_hand_model(hand_model_mm, MM_TO_M)
+                self._skel_cache = (key, InputSkeletonData(
                     joint_rotation_axes=hm.joint_rotation_axes.float().to(dev),
                     joint_rest_positions=hm.joint_rest_positions.float().to(dev)))
             skel = self._skel_cache[1]

@@ -38,12 +38,19 @@ class InputFrameData:
 @dataclass
 class InputFrameDesc:
     """sample_range [bs,2] (start,end image index, 1 or 2 views); memory_idx [bs]; use_memory
-    [bs] bool; hand_idx [bs] (1 = right hand)."""
+    [bs] bool; hand_idx [bs] (1 = right hand).
+
+    `n_memory_slots` is an optional extension: the caller's promise that every memory_idx is below
+    it.  The reference reads `max(memory_idx) + 1` on the host at every call to grow its memory bank
+    (lib/models/temporal.py:101-123); with the promise the bank is sized without that device->host
+    read.  A broken promise does not corrupt memory: the sample runs without recurrent memory and
+    UMT_STATUS_MEMORY_INDEX is raised by `UmeTrackModel.check_status()`."""
 
     sample_range: torch.Tensor
     memory_idx: torch.Tensor
     use_memory: torch.Tensor
     hand_idx: torch.Tensor
+    n_memory_slots: Optional[int] = None
 
 
 @dataclass
@@ -103,8 +110,6 @@ class UmeTrackModel:
         self._mem_features = torch.empty(0)
         self._prev_extrinsics = torch.empty(0)
         self.last_launch_count = 0
-        self._mem_key = None
-        self._mem_need = 0
 
     # ---- nn.Module-like surface the callers use ----------------------------------------------
     def eval(self):
@@ -232,13 +237,18 @@ class UmeTrackModel:
         if bs == 0:
             raise ValueError("empty batch")
         self._ensure_workspace(8 if features is not None else n_img, bs)
-        # the reference reads max(memory_idx) on the host every call (temporal.py:101); do it once
-        # per distinct index tensor so a steady-state loop has no host sync
-        key = (mem_idx.data_ptr(), mem_idx._version, mem_idx.numel())
-        if key != self._mem_key:
-            self._mem_need = int(mem_idx.max().item()) + 1
-            self._mem_key = key
-        self._grow_memory(self._mem_need)
+        # memory bank size: like the reference, max(memory_idx) + 1 read on the host at every call
+        # (temporal.py:101) -- from the caller's tensor if that is still on the host, which costs
+        # nothing -- unless the caller states the slot count (InputFrameDesc.n_memory_slots)
+        if frame_desc.n_memory_slots is not None:
+            need = int(frame_desc.n_memory_slots)
+        elif frame_desc.memory_idx.device.type == "cpu":
+            need = int(frame_desc.memory_idx.max()) + 1
+        else:
+            need = int(mem_idx.max().item()) + 1
+        if need < 1:
+            raise ValueError("memory_idx must be non-negative")
+        self._grow_memory(need)
         dev = self._device
         ja = torch.empty((bs, 22), dtype=torch.float32, device=dev)
         wr = torch.empty((bs, 4, 4), dtype=torch.float32, device=dev)
@@ -330,6 +340,22 @@ class UmeTrackModel:
                 native.current_stream_ptr()), "umt_model_tail_scan")
         self.last_launch_count = lib.umt_model_last_launch_count(self._handle)
         return ja, wr, sg
+
+    def check_status(self) -> None:
+        """Raise if a kernel recorded a condition since the last check: a memory index outside the
+        bank (only possible with a wrong `n_memory_slots` promise or a too small `n_slots`), or an
+        fp16-mode activation outside the half range.  Synchronises the current stream."""
+        self._require_handle()
+        st = ctypes.c_uint(0)
+        with torch.cuda.device(self._device):
+            native.check(native.lib().umt_model_status(self._handle, ctypes.byref(st), native.current_stream_ptr()),
+                         "umt_model_status")
+        if st.value & native.STATUS_MEMORY_INDEX:
+            raise native.NativeError("a memory_idx was outside the memory bank: that sample ran without "
+                                     "recurrent memory (n_memory_slots / n_slots too small)")
+        if st.value & native.STATUS_FP16_RANGE:
+            raise native.NativeError("fp16 mode: an activation left the half range (|x| > 65504); "
+                                     "use set_mode('fp32') or 'bf16' for these weights")
 
     # ---- extras ----------------------------------------------------------------------------
     def encode(self, images: torch.Tensor) -> torch.Tensor:

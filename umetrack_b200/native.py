@@ -17,6 +17,8 @@ MODE_FP16 = 2
 HEAD_KNOWN = 0
 HEAD_UNKNOWN = 1
 RESAMPLE_PARAMS = 48
+STATUS_MEMORY_INDEX = 1
+STATUS_FP16_RANGE = 2
 
 # every symbol the header declares: (name, restype, argtypes)
 SIGNATURES = {
@@ -43,7 +45,9 @@ SIGNATURES = {
     "umt_model_encode": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_encode_static": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_last_launch_count": (c_int, [c_void_p]),
+    "umt_model_status": (c_int, [c_void_p, POINTER(ctypes.c_uint), c_void_p]),
     "umt_model_profile_layers": (c_int, [c_void_p, c_int, c_void_p, c_int, POINTER(c_float), c_void_p]),
+    "umt_model_debug_halo_check": (c_int, [c_void_p, POINTER(ctypes.c_longlong), c_void_p]),
     "umt_model_debug_layer": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p,
                                       POINTER(c_int), c_void_p]),
     "umt_fk_landmarks": (c_int, [c_void_p] * 8 + [c_int, c_void_p, c_void_p]),

@@ -151,11 +151,13 @@ def load_hand_model_json(path: str) -> dict:
 
 def make_recording(hand_model_dict: dict, seed: int = 0, n_frames: int = 32,
                    width: int = 640, height: int = 480, smooth_images: bool = False,
-                   dropouts: bool = True, with_frames: bool = True):
+                   dropouts: bool = True, with_frames: bool = True, presence=None):
     """Synthetic recording: (labels_dict in the reference JSON schema, frames uint8
     [T, H, 4*W]).  Both hands move on smooth trajectories 250-450 mm in front of the rig;
     joint angles stay inside `joint_limits`; a few confidence dropouts exercise the tracker's
-    history reset; frames are seeded noise (optionally box-blurred)."""
+    history reset; frames are seeded noise (optionally box-blurred).  `presence` ([T,2] of 0/1),
+    if given, replaces the hand confidences (e.g. one hand only for a stretch of frames); it does
+    not change any other generated value."""
     g = np.random.default_rng([seed, 11])
     cams, angles, cam_xf = make_rig(seed, width, height)
     limits = np.asarray(hand_model_dict["joint_limits"], dtype=np.float64)
@@ -188,6 +190,8 @@ def make_recording(hand_model_dict: dict, seed: int = 0, n_frames: int = 32,
     if dropouts and T >= 12:
         conf[T // 3, 0] = 0.0
         conf[T // 2: T // 2 + 2, 1] = 0.0
+    if presence is not None:
+        conf = np.asarray(presence, dtype=np.float64).reshape(T, 2).copy()
     frames = g.integers(0, 256, size=(T, height, 4 * width), dtype=np.uint8) if with_frames else None
     if smooth_images and frames is not None:
         f = frames.astype(np.float32)

@@ -309,7 +309,7 @@ def eval_sequences(model, inputs: Sequence[Dict[str, Any]], seq_mode: str = "mul
                             intrinsics=torch.flatten(intr[:, t, 0:nv], 0, 1).contiguous(),
                             extrinsics_xf=torch.flatten(extr[:, t, 0:nv], 0, 1).contiguous())
         desc = InputFrameDesc(hand_idx=hand_idx[:, t].long(), sample_range=sample_range, memory_idx=memory_idx,
-                              use_memory=use_memory)
+                              use_memory=use_memory, n_memory_slots=bs)
         if use_skel:
             out = model.regress_pose_use_skeleton(fd, desc, InputSkeletonData(
                 joint_rotation_axes=left_hm.joint_rotation_axes[:, t].contiguous(),
