@@ -50,22 +50,35 @@ def conv_flops_per_crop():
 
 def ncu_conv_traffic(mode):
     """dram__bytes_read + dram__bytes_write per conv_umma_kernel launch, averaged over the 24
-    backbone launches of the committed `ncu --set full` capture (fp16 mode, 4096 crops per launch);
-    None for the other modes or if the summary is missing.  Bytes per launch, like `achieved`."""
-    path = os.path.join(ROOT, "profiles", "r01_ncu_conv_full_summary_v6.csv")
-    if mode != "fp16" or not os.path.exists(path):
-        return None
+    backbone launches of the newest committed `ncu --set full` capture of this numeric mode
+    (profiles/r*_ncu_conv_full_summary_<mode>.csv, 4096 crops per launch); None if there is none.
+    Bytes per launch, like `achieved`."""
     import csv
-    tot, n = 0.0, 0
-    for r in csv.reader(open(path)):
-        if len(r) <= 6 or "conv_umma_kernel<" not in r[0]:
-            continue
-        targs = [int(v) for v in r[0].split("<")[1].split(">")[0].replace("true", "1").replace("false", "0").split(",")]
-        if targs[0] in (32, 64, 128, 256) and targs[1] == 2 and targs[2] != 2:     # backbone, fp16 mode
-            tot += float(r[5]) * 1e9 + float(r[6]) * 1e6   # columns: read [Gbyte], write [Mbyte]
-            n += 1
-    return {"bytes_per_launch": tot / n, "launches": n, "crops_per_launch": 4096,
-            "source": "profiles/r01_ncu_conv_full_summary_v6.csv"} if n else None
+    import glob
+    mode_id = {"fp32": 0, "bf16": 1, "fp16": 2}[mode]
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", f"r*_ncu_conv_full_summary_{mode}.csv")), reverse=True):
+        tot, n, crops = 0.0, 0, 4096
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        rd = wr = None
+        for r in csv.reader(open(path)):
+            if r and r[0].startswith("# crops_per_launch"):
+                crops = int(r[1])
+            if r and r[0].startswith("Kernel Name"):
+                for i, h in enumerate(r):
+                    if h.startswith("dram__bytes_read.sum"):
+                        rd = (i, scale[h.split("[")[1].rstrip("]")])
+                    if h.startswith("dram__bytes_write.sum"):
+                        wr = (i, scale[h.split("[")[1].rstrip("]")])
+            if len(r) <= 6 or "conv_umma_kernel<" not in r[0] or rd is None or wr is None:
+                continue
+            targs = [int(v) for v in r[0].split("<")[1].split(">")[0].replace("true", "1").replace("false", "0").split(",")]
+            if targs[0] in (32, 64, 128, 256) and targs[1] == mode_id and targs[2] != 2:     # backbone launches of this mode
+                tot += float(r[rd[0]]) * rd[1] + float(r[wr[0]]) * wr[1]
+                n += 1
+        if n:
+            return {"bytes_per_launch": tot / n, "launches": n, "crops_per_launch": crops,
+                    "source": os.path.relpath(path, ROOT)}
+    return None
 
 
 class ClockSampler:
@@ -263,18 +276,90 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def recordings_sharded(model, hm_dict, dev, rank, world, n_rec, n_frames, group=8):
+    """BASELINE configs[4]: `n_rec` synthetic recordings (seeds 0..n_rec-1, `n_frames` frames, 4 fisheye
+    views, both hands, dropouts) sharded by recording over the ranks (longest-processing-time first),
+    every rank running the batched driver on its shard -- crop cameras, resampling, encoder, time
+    scan, FK, MPJPE / acceleration sums -- and ONE all-reduce of the metric sums at the end
+    (run_eval_known_skeleton.py:113-119 is a Pool(8).map over recordings followed by a concatenate).
+    Frames are seeded noise generated on the device ("decoded frames staged to the GPU"); labels are
+    the reference's JSON schema.  Returns the stage record; collective: every rank must call it."""
+    import torch
+    import torch.distributed as dist
+
+    from umetrack_b200 import synthetic
+    from umetrack_b200.batched import track_recordings_batched
+    from umetrack_b200.metrics import MetricSums, shard_indices
+
+    H, W4 = 480, 2560
+
+    def frames_of(r):
+        g = torch.Generator(device=dev).manual_seed(7000 + r)
+        return torch.randint(0, 256, (n_frames, H, W4), dtype=torch.uint8, device=dev, generator=g)
+
+    def run(indices, sums):
+        n_valid = 0
+        for i0 in range(0, len(indices), group):
+            recs = [(synthetic.make_recording(hm_dict, seed=r, n_frames=n_frames, with_frames=False)[0], frames_of(r))
+                    for r in indices[i0:i0 + group]]
+            res = track_recordings_batched(model, recs, sums=sums)
+            n_valid += int(sum(x["valid_tracking"].sum() for x in res))
+        return n_valid
+
+    mine = shard_indices(n_rec, rank, world, costs=[n_frames] * n_rec)
+    run(mine[:1], MetricSums(dev))                       # warm-up (allocations, lazy module load)
+    sums = MetricSums(dev)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    n_valid = run(mine, sums)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt, float(n_valid)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tm = t[:1].clone()
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)          # time: max over ranks
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)           # hand-frames: sum over ranks
+        t[0] = tm[0]
+    sums.all_reduce()                                      # the path's only collective (NCCL)
+    res = sums.result()
+    out = {"recordings": n_rec, "frames_each": n_frames, "hand_frames": int(t[1].item()), "wall_s": float(t[0].item()),
+           "hand_frames_per_s": float(t[1].item() / t[0].item()), "ranks": world,
+           "recordings_per_rank": [len(shard_indices(n_rec, r, world, costs=[n_frames] * n_rec)) for r in range(world)],
+           "mpjpe_mm": res["mpjpe"], "mpjpa": res["mpjpa"], "gt_mpjpa": res["gt_mpjpa"],
+           "note": "host loop included; frames generated on the device, labels on the host; "
+                   "time = max over ranks, hand-frames = sum over ranks, metric sums all-reduced once"}
+    if world > 1 and rank == 0:
+        # the same recordings on ONE GPU (untimed): the all-reduced means must agree within 0.01
+        one = MetricSums(dev)
+        run(list(range(n_rec)), one)
+        r1 = one.result()
+        out["single_gpu_check"] = {"mpjpe_mm": r1["mpjpe"], "mpjpa": r1["mpjpa"],
+                                   "abs_delta_mpjpe": abs(r1["mpjpe"] - res["mpjpe"]),
+                                   "abs_delta_mpjpa": abs(r1["mpjpa"] - res["mpjpa"]),
+                                   "within_0.01": bool(abs(r1["mpjpe"] - res["mpjpe"]) < 0.01
+                                                       and abs(r1["mpjpa"] - res["mpjpa"]) < 0.01)}
+    if world > 1:
+        dist.barrier()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=2048, help="hand-frames per step per GPU")
-    ap.add_argument("--mode", default="fp16", choices=["fp32", "bf16", "fp16"],
-                    help="encoder numeric mode: fp16 (default; 16-bit operands, fp32 accumulate, parity-tested), "
-                         "fp32 (split-bf16 x3, fp32-equivalent) or bf16")
+    ap.add_argument("--mode", default="fp32", choices=["fp32", "bf16", "fp16"],
+                    help="encoder numeric mode of the headline: fp32 (default; split-bf16 x3, fp32-equivalent = the "
+                         "reference's precision), fp16 or bf16 (16-bit operands, fp32 accumulate; reported under `modes`)")
     ap.add_argument("--chunk", type=int, default=4096, help="crops per encoder pass (workspace size)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stages", action="store_true", help="skip the per-stage and recording measurements")
+    ap.add_argument("--sharded-recordings", type=int, default=64)
+    ap.add_argument("--sharded-frames", type=int, default=256)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -309,10 +394,14 @@ def main():
     model = UmeTrackModel(synthetic.make_state_dict(0), chunk_images=args.chunk).to(dev)
     model.set_mode(args.mode)
     host = synthetic.make_model_batch(B, seed=1234 + rank)
-    pinned = {k: v.pin_memory() for k, v in host.items()}
+    # crops as cv2.remap leaves them: uint8.  The device-resident leg takes the float32 crops the
+    # reference's model API takes ([0,1], tracker.py:211); the end-to-end leg uploads the uint8 crops.
+    crops_u8 = (host["left_images"] * 255.0).round().to(torch.uint8)
+    host["left_images"] = crops_u8.float() / 255.0
     d = {k: v.to(dev) for k, v in host.items()}
+    pinned = {k: (crops_u8 if k == "left_images" else v).pin_memory() for k, v in host.items()}
     fd = InputFrameData(d["left_images"], d["intrinsics"], d["extrinsics_xf"])
-    desc = InputFrameDesc(d["sample_range"], d["memory_idx"], d["use_memory"], d["hand_idx"])
+    desc = InputFrameDesc(d["sample_range"], d["memory_idx"], d["use_memory"], d["hand_idx"], n_memory_slots=B)
     skel = InputSkeletonData(hm.joint_rotation_axes.float()[None].to(dev),
                              (hm.joint_rest_positions * 1e-3).float()[None].to(dev))
     g = np.random.default_rng(99)
@@ -332,14 +421,6 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-
-    # ---- warm-up (first step starts with empty memory, like the first frame of a recording) ----
-    d["use_memory"][:] = False
-    device_step(fd, desc)
-    d["use_memory"][:] = True
-    for _ in range(W - 1):
-        device_step(fd, desc)
-    launches = model.last_launch_count + 2
 
     def timed(fn, collective=True):
         """K steps between CUDA events; with `collective`, bracketed by barriers and reduced to the
@@ -363,19 +444,11 @@ def main():
             barrier()
         return ms
 
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    time.sleep(0.3)
-    t_wall0 = time.time()
-    ms_total = timed(lambda: device_step(fd, desc))
-    t_wall1 = time.time()
-    clocks = sampler.stop(t_wall0, t_wall1)
-    value = world * B * K / (ms_total * 1e-3)
-
-    # ---- end to end through the public API: pinned host inputs in, keypoints out, every step.
-    # The host->device copy of step i+1 runs on a copy stream while step i computes (two device
-    # input slots), the way a user feeding the model from a loader would write it; every timed step
-    # still moves its own inputs (h2d_bytes_per_step) and results (d2h_bytes_per_step). ----
+    # ---- end to end through the public API: pinned host inputs (uint8 crops + descriptors) in,
+    # keypoints out, every step.  The host->device copy of step i+1 runs on a copy stream while step
+    # i computes (two device input slots), the way a user feeding the model from a loader would write
+    # it; every timed step still moves its own inputs (h2d_bytes_per_step) and results
+    # (d2h_bytes_per_step). ----
     out_host = torch.empty((B, 21, 3), dtype=torch.float32).pin_memory()
     copy_stream = torch.cuda.Stream(device=dev)
     slots = [{k: torch.empty_like(v, device=dev) for k, v in pinned.items()} for _ in range(2)]
@@ -397,40 +470,74 @@ def main():
         torch.cuda.current_stream().wait_event(ready[slot])
         dd = slots[slot]
         kp = device_step(InputFrameData(dd["left_images"], dd["intrinsics"], dd["extrinsics_xf"]),
-                         InputFrameDesc(dd["sample_range"], dd["memory_idx"], dd["use_memory"], dd["hand_idx"]))
+                         InputFrameDesc(dd["sample_range"], dd["memory_idx"], dd["use_memory"], dd["hand_idx"],
+                                        n_memory_slots=B))
         consumed[slot].record()
         out_host.copy_(kp, non_blocking=True)
 
     pinned["use_memory"][:] = True
-    for ev in consumed:
-        ev.record()
-    stage_inputs(0)
-    e2e_step()
-    ms_e2e = timed(e2e_step)
-    e2e_value = world * B * K / (ms_e2e * 1e-3)
     h2d = sum(v.numel() * v.element_size() for v in pinned.values())
     d2h = out_host.numel() * out_host.element_size()
+
+    def measure_mode(mode, collective):
+        """(device-resident hand-frames/s, end-to-end hand-frames/s, ms per step, e2e ms per step,
+        launches per step) of one numeric mode; recurrent memory in steady state."""
+        model.set_mode(mode)
+        d["use_memory"][:] = False            # first step starts with empty memory, like a recording's first frame
+        device_step(fd, desc)
+        d["use_memory"][:] = True
+        for _ in range(W - 1):
+            device_step(fd, desc)
+        launches = model.last_launch_count + 4           # + FK, MPJPE sum, per-frame errors, PCK counts
+        ms = timed(lambda: device_step(fd, desc), collective)
+        state["i"] = 0
+        for ev in consumed:
+            ev.record()
+        stage_inputs(0)
+        e2e_step()
+        ms_e2e = timed(e2e_step, collective)
+        n = world if collective else 1
+        return n * B * K / (ms * 1e-3), n * B * K / (ms_e2e * 1e-3), ms / K, ms_e2e / K, launches
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.3)
+    t_wall0 = time.time()
+    value, e2e_value, ms_step, ms_e2e_step, launches = measure_mode(args.mode, True)
+    t_wall1 = time.time()
+    clocks = sampler.stop(t_wall0, t_wall1)
+    model.check_status()
 
     sums.all_reduce()   # the only collective on the path: NCCL all-reduce of the metric sums
     metrics = sums.result()
 
+    dtype = {"fp32": "bf16x3 (split-bf16 operands, three tensor-core products per MAC, fp32 accumulate: "
+                     "fp32-equivalent, the reference's precision)",
+             "bf16": "bf16 (fp32 accumulate)", "fp16": "fp16 (fp32 accumulate)"}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": {"fp32": "bf16x3 (split-bf16 operands, fp32 accumulate; fp32-equivalent)", "bf16": "bf16",
-                  "fp16": "fp16 (fp32 accumulate)"}[args.mode],
-        "data": "synthetic",
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": dtype[args.mode], "data": "synthetic",
         "config": {"workload": "configs[3] synthetic throughput: 96x96 crops -> keypoints, known-skeleton head, "
                                "memory steady state", "hand_frames_per_step_per_gpu": B, "crops_per_hand_frame": 2,
                    "crops_per_sec": 2 * value, "numeric_mode": args.mode,
-                   "l2": "inputs (151 MB of crops at B=2048) and activations exceed the 126 MB L2; no flush",
+                   "l2": "inputs (151 MB of float32 crops at B=2048) and activations exceed the 126 MB L2; no flush",
                    "sharding": "independent batches per rank, NCCL all-reduce of metric sums only"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": ms_e2e / K},
+                "ms_per_step": ms_e2e_step,
+                "inputs": "uint8 crops (as cv2.remap leaves them; /255 on the device) + float32 camera parameters + "
+                          "int64 descriptors from pinned host memory; float32 keypoints back"},
         "gpu_launches": launches * K,
         "clocks": clocks,
         "mpjpe_vs_synthetic_gt_mm": metrics["mpjpe"],
     }
+
+    # ---- BASELINE configs[4]: recordings sharded over the ranks (collective) ----
+    sharded = None
+    if not args.no_stages and args.sharded_recordings > 0:
+        model.set_mode(args.mode)
+        sharded = recordings_sharded(model, hm_dict, dev, rank, world, args.sharded_recordings, args.sharded_frames)
+        model.reset_memory()
 
     if rank == 0:
         # ---- roofline of the dominant kernel family: the 24 tcgen05 convolutions ----
@@ -439,9 +546,11 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        peak_tf = peaks.get("bf16_tflops_sustained") or 1400.0
-        peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if peaks else "fallback 1.4 PFLOP/s sustained"
-        n_prof = min(d["left_images"].shape[0], 2048)
+        burst = peaks.get("bf16_tflops") or 1590.0
+        sustained = peaks.get("bf16_tflops_sustained") or 1400.0
+        src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback (B200_PROFILING.md: 1.59 PFLOP/s burst, 1.4 sustained)"
+        model.set_mode(args.mode)
+        n_prof = min(d["left_images"].shape[0], args.chunk)      # the crops one encoder launch of the step processes
         reps = 3
         acc = np.zeros(26)
         model.profile_layers(d["left_images"][:n_prof])
@@ -451,51 +560,79 @@ def main():
         flops = np.array(conv_flops_per_crop(), dtype=np.float64) * n_prof
         conv_ms = acc[1:25]
         achieved = flops.sum() / (conv_ms.sum() * 1e-3) / 1e12
-        executed = achieved * (3 if args.mode == "fp32" else 1)
+        products = 3 if args.mode == "fp32" else 1
+        traffic = ncu_conv_traffic(args.mode)
+        step_tflops = value / world * 1.957607712e9 / 1e12
         line["roofline"] = {
-            "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-            "frac": achieved / peak_tf,
-            "traffic": (ncu_conv_traffic(args.mode) or {}).get("bytes_per_launch"),
-            "traffic_source": ncu_conv_traffic(args.mode),
+            "bound": "tensor", "achieved": achieved, "peak": burst, "unit": "TFLOP/s",
+            "frac": achieved / burst,
+            "peak_sustained": sustained, "frac_vs_sustained": achieved / sustained,
+            "traffic": (traffic or {}).get("bytes_per_launch"),
+            "traffic_source": traffic,
             "kernel": "conv_umma_kernel (24 launches per encoder pass)",
-            "peak_source": peak_src,
-            "note": "achieved = algorithmic conv FLOPs / sum of the 24 launch durations (CUDA events inside "
-                    "umt_model_profile_layers); the fp32-equivalent mode executes 3 tensor-core products per "
-                    "algorithmic MAC",
-            "executed_tensor_tflops": executed, "executed_frac": executed / peak_tf,
+            "peak_source": src + ": `peak` is the bf16 burst figure because the launches are timed one by one with "
+                                 "CUDA events at burst clocks (see `clocks`); the sustained figure is given beside it",
+            "note": "achieved = algorithmic conv FLOPs (962.6 MFLOP per crop x crops per launch) / sum of the 24 launch "
+                    "durations (CUDA events between launches, umt_model_profile_layers, same crops per launch as the "
+                    "timed step); the fp32-equivalent mode executes 3 bf16 tensor-core products per algorithmic MAC, "
+                    "so its ceiling on this scale is 1/3",
+            "tensor_products_per_mac": products,
+            "executed_tensor_tflops": achieved * products, "executed_frac": achieved * products / burst,
+            "executed_frac_vs_sustained": achieved * products / sustained,
+            "whole_step_tflops": step_tflops, "whole_step_frac": step_tflops / burst,
+            "whole_step_frac_vs_sustained": step_tflops / sustained,
             "conv_ms_per_pass": float(conv_ms.sum()), "stem_ms": float(acc[0]), "proj_ms": float(acc[25]),
             "crops_per_pass": n_prof,
             "per_layer_tflops": [float(f / (t * 1e-3) / 1e12) for f, t in zip(flops, conv_ms)],
         }
-        # ---- the other numeric modes, for the tolerance report (BASELINE.json configs[3]): one GPU,
-        # same batch, same recurrent state; keypoint deltas are against the fp32-equivalent mode ----
-        mem_a = model._mem_features.clone()
+        # ---- every numeric mode as a first-class record (BASELINE.json configs[3]: 16-bit encoder vs fp32
+        # tolerance check): device-resident and end-to-end rate on this GPU, keypoint deltas against the
+        # fp32-equivalent mode from the same recurrent state ----
         model.set_mode("fp32")
-        kp_ref = device_step(fd, desc).clone()
-        line["other_modes"] = []
-        for other in ("fp32", "bf16", "fp16"):
-            if other == args.mode:
-                continue
-            model.set_mode(other)
-            device_step(fd, desc)
-            ms_o = timed(lambda: device_step(fd, desc), collective=False)   # rank 0 only: no collectives here
+        d["use_memory"][:] = False               # (the recordings stage reset the memory bank: refill it)
+        device_step(fd, desc)
+        d["use_memory"][:] = True
+        device_step(fd, desc)
+        mem_a, ext_a = model._mem_features.clone(), model._prev_extrinsics.clone()
+
+        def restore():
             model._mem_features.copy_(mem_a)
-            kp_b = device_step(fd, desc)
-            line["other_modes"].append({"numeric_mode": other, "value": B * K / (ms_o * 1e-3), "unit": UNIT,
-                                        "n_gpus": 1,
-                                        "keypoint_delta_vs_fp32_mm_max": float((kp_ref - kp_b).abs().max()),
-                                        "keypoint_delta_vs_fp32_mm_mean": float((kp_ref - kp_b).abs().mean())})
+            model._prev_extrinsics.copy_(ext_a)
+
+        model.set_mode("fp32")
+        restore()
+        kp_ref = device_step(fd, desc).clone()
+        line["modes"] = {}
+        for mode in ("fp32", "fp16", "bf16"):
+            if mode == args.mode and world == 1:
+                v, e, ms1, ms2, _ = value, e2e_value, ms_step, ms_e2e_step, launches
+            else:
+                v, e, ms1, ms2, _ = measure_mode(mode, False)      # rank 0 only: no collectives here
+            model.set_mode(mode)
+            restore()
+            kp_m = device_step(fd, desc)
+            line["modes"][mode] = {"dtype": dtype[mode], "value": v, "e2e": e, "unit": UNIT, "n_gpus": 1,
+                                   "ms_per_step": ms1, "e2e_ms_per_step": ms2,
+                                   "keypoint_delta_vs_fp32_mm_max": float((kp_ref - kp_m).abs().max()),
+                                   "keypoint_delta_vs_fp32_mm_mean": float((kp_ref - kp_m).abs().mean()),
+                                   "keypoint_gate_mm": 0.05}
         model.set_mode(args.mode)
-        model._mem_features.copy_(mem_a)
-        kp_m = device_step(fd, desc)
-        line["keypoint_delta_vs_fp32_mm_max"] = float((kp_ref - kp_m).abs().max())
-        line["stages"] = measure_stages(model, hm, hm_dict, dev, peaks)
+        restore()
+        try:
+            model.check_status()
+            line["status_flags"] = "clear"
+        except Exception as e:  # noqa: BLE001
+            line["status_flags"] = str(e)
+        if not args.no_stages:
+            line["stages"] = measure_stages(model, hm, hm_dict, dev, peaks)
+            if sharded is not None:
+                line["stages"]["recordings_sharded"] = sharded
         if world == 1 and not args.no_cpu_baseline:
-            rate, cores, _ = cpu_oracle_rate(steps=2, warmup=1)
+            rate, cores, _ = cpu_oracle_rate(steps=5, warmup=2)
             line["cpu_baseline"] = {
                 "value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                "sample": f"2 steps of {CPU_SAMPLE_BATCH} hand-frames (crops->keypoints, torch fp32 model + FK) "
-                          f"after 1 warm-up step, {cores} threads"}
+                "sample": f"5 steps of {CPU_SAMPLE_BATCH} hand-frames (crops->keypoints, torch fp32 model + FK) "
+                          f"after 2 warm-up steps, {cores} threads"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

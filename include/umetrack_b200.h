@@ -153,6 +153,18 @@ int umt_model_forward(umt_model* m, int mode, int head, const float* images,
                       float* mem_state, float* prev_extr, int n_slots, float* out_joint_angles,
                       float* out_wrist, float* out_scale, float* out_sigma, void* stream);
 
+/* umt_model_forward on uint8 crops [n_img,96,96] (16-byte aligned), as cv2.remap leaves them: the
+ * `crop.astype(np.float32) / 255.0` of HandTracker._make_inputs (lib/tracker/tracker.py:211) runs on
+ * the device (IEEE division, identical values), so a host feeding crops uploads one byte per pixel
+ * instead of four. */
+int umt_model_forward_u8(umt_model* m, int mode, int head, const uint8_t* images_u8,
+                         const float* intrinsics, const float* extrinsics,
+                         const int64_t* sample_range, const int64_t* memory_idx,
+                         const uint8_t* use_memory, const int64_t* hand_idx, int n_img,
+                         int n_samples, const float* skel_axes, const float* skel_rest, int n_skel,
+                         float* mem_state, float* prev_extr, int n_slots, float* out_joint_angles,
+                         float* out_wrist, float* out_scale, float* out_sigma, void* stream);
+
 /* Everything after the backbone: same arguments as umt_model_forward with the per-crop
  * `features` [n_img,72,6,6] (from umt_model_encode) in place of the images.  The backbone has no
  * temporal dependency, so a whole recording can be encoded in one batch and this entry point
@@ -184,6 +196,10 @@ int umt_model_tail_scan(umt_model* m, int head, const float* features, const flo
  * (`_image_backbone`, lib/models/model_utils.py:107-138).  Uses the bound workspace. */
 int umt_model_encode(umt_model* m, int mode, const float* images, int n_img, float* features,
                      void* stream);
+
+/* umt_model_encode on uint8 crops (see umt_model_forward_u8). */
+int umt_model_encode_u8(umt_model* m, int mode, const uint8_t* images_u8, int n_img, float* features,
+                        void* stream);
 
 /* Backbone for callers that cannot allocate device memory.  [No counterpart in the reference,
  * which is Python and lets torch allocate.]  Same result as umt_model_encode for n_img <= 4

@@ -172,3 +172,22 @@ def test_out_of_range_memory_index_is_reported():
     with pytest.raises(native.NativeError, match="memory_idx"):
         model.check_status()
     model.check_status()                       # the flag is cleared by the read
+
+
+def test_uint8_crops_give_the_same_result_as_their_float_conversion():
+    """`crop.astype(np.float32) / 255.0` (lib/tracker/tracker.py:211) on the device: identical values,
+    hence bit-identical outputs, for ragged counts over two chunks."""
+    model = UmeTrackModel(synthetic.make_state_dict(0), chunk_images=16).to("cuda")
+    hm = hmod.load_hand_model_from_dict(hm_dict())
+    skel = InputSkeletonData(hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None])
+    b = synthetic.make_model_batch(11, seed=77, single_view_every=4)
+    u8 = (b["left_images"] * 255).round().to(torch.uint8)
+    as_float = torch.from_numpy(u8.numpy().astype(np.float32) / 255.0)
+    assert torch.equal(model.encode(u8.cuda()), model.encode(as_float.cuda()))
+    b["use_memory"][:] = False
+    outs = []
+    for imgs in (u8, as_float):
+        b["left_images"] = imgs
+        fd, desc = _inputs(b)
+        outs.append(model.regress_pose_use_skeleton(fd, desc, skel))
+    assert torch.equal(outs[0].joint_angles, outs[1].joint_angles) and torch.equal(outs[0].wrist_xfs, outs[1].wrist_xfs)

@@ -186,13 +186,23 @@ __device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) {
 // Issue the MMAs of `n` consecutive taps (one weight stage) for all S sub-tiles.  Descriptors are
 // advanced by adding to their low word: +shift rows for a tap, +128 (2048 B) per sub-tile, +slab
 // bytes per tap on the weight side; everything else is loop invariant.
-template <int S, int COUT, bool SPLIT>
+// Split mode, weight slab = [plane 0: hi rows, lo rows][plane 1: hi rows, lo rows], so the hi rows alone
+// (N = COUT) and hi|lo together (N = 2 COUT) are the same descriptor with a different N.
+//   MERGE (COUT <= 112): two MMAs per tap and sub-tile instead of three:
+//       [D1 | D2] += a_hi * [w_hi | w_lo]   (N = 2 COUT)        D1 += a_lo * w_hi   (N = COUT)
+//   and the epilogue adds D1 + D2.  The narrow layers are bound by the shared-memory operand path
+//   (every MMA re-reads its 4 KB A tile), so one A read fewer per tap is 27 % fewer operand bytes.
+template <int S, int COUT, bool SPLIT, bool MERGE>
 __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t0, int n, uint32_t a_lo32,
                                            uint32_t a_hi32, uint32_t a_plane_bytes, uint32_t b_lo32,
                                            uint32_t b_hi32, uint32_t d_base, uint32_t idesc, uint32_t any,
                                            bool skip_hilo) {
   constexpr uint32_t kBHalf16 = (2u * COUT * 16u) >> 4;
   constexpr uint32_t kBSlab16 = SPLIT ? 2u * kBHalf16 : kBHalf16;
+  constexpr uint32_t kLoRows16 = COUT;                           // lo rows follow the hi rows inside a plane (16-byte units)
+  constexpr uint32_t kDCols = MERGE ? 2u * COUT : (uint32_t)COUT;   // accumulator columns per sub-tile
+  constexpr uint32_t kIdescWide = (uint32_t)((2 * COUT) >> 3) << 17;
+  constexpr uint32_t kIdescNMask = 0x3Fu << 17;
   const uint32_t a_lo_plane16 = (2u * a_plane_bytes) >> 4;
   const int tap0 = P.st_tap0[stage] + t0;
 #pragma unroll 1
@@ -201,16 +211,22 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
     const uint32_t shift16 = (uint32_t)((int)P.tap_shift[tap0 + j] - P.lo_shift + (int)P.tap_src[tap0 + j] * P.patch_rows);
     const uint32_t a0 = a_lo32 + shift16;
     const uint64_t b_hi = desc64(b_lo32 + (uint32_t)j * kBSlab16, b_hi32);
-    const uint64_t b_lo = desc64(b_lo32 + (uint32_t)j * kBSlab16 + kBHalf16, b_hi32);
+    const uint64_t b_lo = desc64(b_lo32 + (uint32_t)j * kBSlab16 + kLoRows16, b_hi32);
 #pragma unroll
     for (int s = 0; s < S; ++s) {
       const uint64_t a_hi = desc64(a0 + (uint32_t)s * 128u, a_hi32);
-      const uint32_t d = d_base + (uint32_t)(s * COUT);
-      tc_mma_bf16(d, a_hi, b_hi, idesc, any);
-      if (SPLIT) {
+      const uint32_t d = d_base + (uint32_t)s * kDCols;
+      if (MERGE) {
         const uint64_t a_lo = desc64(a0 + (uint32_t)s * 128u + a_lo_plane16, a_hi32);
-        if (!skip_hilo) tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
+        tc_mma_bf16(d, a_hi, b_hi, skip_hilo ? idesc : ((idesc & ~kIdescNMask) | kIdescWide), any);
         tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
+      } else {
+        tc_mma_bf16(d, a_hi, b_hi, idesc, any);
+        if (SPLIT) {
+          const uint64_t a_lo = desc64(a0 + (uint32_t)s * 128u + a_lo_plane16, a_hi32);
+          if (!skip_hilo) tc_mma_bf16(d, a_hi, b_lo, idesc, 1u);
+          tc_mma_bf16(d, a_lo, b_hi, idesc, 1u);
+        }
       }
     }
     any = 1u;
@@ -232,6 +248,8 @@ template <int COUT, int MODE, int EPI>
 __global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma_kernel(const __grid_constant__ ConvParams P) {
   constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
+  constexpr bool MERGE = SPLIT && COUT <= 112;              // see issue_taps
+  constexpr int kDCols = MERGE ? 2 * COUT : COUT;           // accumulator columns per sub-tile
   extern __shared__ __align__(128) uint8_t smem[];
   // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -264,7 +282,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
   const uint16_t cta_mask = (uint16_t)((1u << cl) - 1u);
   const int mc = P.S * 128;
-  const uint32_t buf_cols = (uint32_t)(P.S * COUT);
+  const uint32_t buf_cols = (uint32_t)(P.S * kDCols);
   const uint32_t want_cols = buf_cols * (uint32_t)n_buf;
   const uint32_t tmem_cols = want_cols <= 32u ? 32u : want_cols <= 64u ? 64u : want_cols <= 128u ? 128u
                              : want_cols <= 256u ? 256u : 512u;
@@ -359,7 +377,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     const bool leader = elect_one();
     const uint64_t desc_hi_bits = ((uint64_t)((128u >> 4) & 0x3FFF) << 32) | (1ull << 46);
     const uint64_t a_desc_base = desc_hi_bits | ((uint64_t)((a_plane_bytes >> 4) & 0x3FFF) << 16);
-    const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)(((COUT * 16u) >> 4) & 0x3FFF) << 16);
+    // plane distance of a weight slab: COUT rows (16-bit modes) or hi + lo rows (split mode)
+    const uint64_t b_desc_base = desc_hi_bits | ((uint64_t)((((SPLIT ? 2u : 1u) * COUT * 16u) >> 4) & 0x3FFF) << 16);
     int it = 0, kb = 0, tc = 0;
     long long w_acc = 0, w_a = 0, w_b = 0, t_begin = clock64();
     unsigned long long g_begin = 0;
@@ -396,9 +415,9 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
           const uint32_t b_hi32 = (uint32_t)(b_desc_base >> 32);
           if (leader) {
             switch (P.S) {
-              case 1: issue_taps<1, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-              case 2: issue_taps<2, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
-              default: issue_taps<4, COUT, SPLIT>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              case 1: issue_taps<1, COUT, SPLIT, MERGE>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              case 2: issue_taps<2, COUT, SPLIT, MERGE>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
+              default: issue_taps<4, COUT, SPLIT, MERGE>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
             }
             if (cl == 1) tc_commit(b_empty(bslot));
             else tc_commit_multicast(b_empty(bslot), cta_mask);   // frees the slot in every CTA of the cluster
@@ -430,7 +449,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
       const int buf = tc % n_buf;
       const long long q0 = (long long)tile * mc;
-      constexpr int kStep = (COUT % 32 == 0) ? 32 : 16;   // columns per TMEM round trip
+      constexpr int kStep = (COUT % 32 == 0 && !MERGE) ? 32 : 16;   // columns per TMEM round trip
       constexpr int kRows = kStep / 8;
       // identity residual: the rows of the NEXT chunk are requested before the current chunk is
       // processed (and the first chunk's before the accumulator is awaited)
@@ -474,10 +493,12 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
 #pragma unroll 1
         for (int c0 = 0; c0 < COUT; c0 += kStep) {
           uint32_t v[kStep];
+          uint32_t v2[MERGE ? kStep : 1];   // second accumulator (a_hi * w_lo) of the merged form
           const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) +
-                                 (uint32_t)buf * buf_cols + (uint32_t)(s * COUT + c0);
+                                 (uint32_t)buf * buf_cols + (uint32_t)(s * kDCols + c0);
           tc_ld16(taddr, v);
           if (kStep == 32) tc_ld16(taddr + 16, v + 16);
+          if (MERGE) tc_ld16(taddr + COUT, v2);
           uint4 rc_h[kRows], rc_l[kRows];
           if (EPI == kEpiResidual) {
 #pragma unroll
@@ -491,7 +512,11 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
             for (int h = 0; h < kStep / 8; ++h) {
               float f[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e];
+              for (int e = 0; e < 8; ++e) {
+                f[e] = __uint_as_float(v[h * 8 + e]);
+                if (MERGE) f[e] += __uint_as_float(v2[h * 8 + e]);
+                f[e] += s_bias[c0 + h * 8 + e];
+              }
               if (EPI == kEpiResidual) {
                 float r[8];
                 decode_row8<MODE>(rc_h[h], rc_l[h], r);
@@ -633,7 +658,8 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int mode,
       const long long row = q + P.tap_shift[P.st_tap0[i] + t];
       const uint8_t* w = P.weights + (size_t)k * slab;
       for (int pl = 0; pl < 2; ++pl) {
-        const uint8_t* wb = w + (size_t)pl * cout * 16 + (size_t)co * 16;
+        // split mode: [plane][hi rows | lo rows]; 16-bit modes: [plane][rows]
+        const uint8_t* wb = w + (size_t)pl * (split ? 2 : 1) * cout * 16 + (size_t)co * 16;
         for (int e = 0; e < 8; ++e) {
           const float a = load_elem(T, mode, (2 * P.st_chunk[i] + pl) * 8 + e, row);
           float b;
@@ -641,7 +667,7 @@ __global__ void conv_simt_check_kernel(const ConvParams P, int cout, int mode,
             b = __half2float(reinterpret_cast<const __half*>(wb)[e]);
           } else {
             b = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(wb)[e]);
-            if (split) b += __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(wb + half)[e]);
+            if (split) b += __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(wb + (size_t)cout * 16)[e]);
           }
           acc = fmaf(a, b, acc);
         }
@@ -1023,7 +1049,10 @@ static Folded folded_from(const float* const* t, const std::string& conv, const 
                       bn.empty() ? nullptr : tensor_ptr(t, bn + ".running_var"), cout, cin, ks);
 }
 
-// append one operand slab: [hi: plane0 [cout][8], plane1 [cout][8]] [lo: same]
+// append one operand slab: [plane 0: hi [cout][8], lo [cout][8]] [plane 1: same]
+static inline size_t slab_index(int cout, int pl, int lo, int co, int e) {
+  return (((size_t)pl * 2 + lo) * cout + co) * 8 + e;
+}
 static void pack_slab(std::vector<uint16_t>& blob, const Folded& f, int chunk, int ky, int kx) {
   const size_t base = blob.size();
   blob.resize(base + (size_t)4 * f.cout * 8);
@@ -1034,8 +1063,8 @@ static void pack_slab(std::vector<uint16_t>& blob, const Folded& f, int chunk, i
         const float v = f.w[(((size_t)co * f.cin + ci) * f.ks + ky) * f.ks + kx];
         const uint16_t hi = f2bf(v);
         const uint16_t lo = f2bf(v - bf2f(hi));
-        blob[base + ((size_t)pl * f.cout + co) * 8 + e] = hi;
-        blob[base + (size_t)2 * f.cout * 8 + ((size_t)pl * f.cout + co) * 8 + e] = lo;
+        blob[base + slab_index(f.cout, pl, 0, co, e)] = hi;
+        blob[base + slab_index(f.cout, pl, 1, co, e)] = lo;
       }
 }
 
@@ -1051,7 +1080,7 @@ static void pack_identity_slab(std::vector<uint16_t>& blob, int cout, int chunk)
   for (int pl = 0; pl < 2; ++pl)
     for (int e = 0; e < 8; ++e) {
       const int co = chunk * 16 + pl * 8 + e;
-      blob[base + ((size_t)pl * cout + co) * 8 + e] = 0x3F80;  // bf16(1.0)
+      blob[base + slab_index(cout, pl, 0, co, e)] = 0x3F80;  // bf16(1.0)
     }
 }
 
@@ -1187,7 +1216,8 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
   p.occ = occ;
   p.bgroup = std::max(1, std::min(9, G));
   p.cluster = std::max(1, std::min(2, clu));
-  p.patch_rows = S * 128 + hi - lo;
+  p.halo_rows = hi - lo;
+  p.patch_rows = S * 128 + p.halo_rows;
   p.phase_out = L.phase_out;
   L.n_slabs = (int)(blob.size() / ((size_t)4 * L.cout * 8));
   std::vector<float> bias = main.b;
@@ -1199,7 +1229,9 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     const size_t half = (size_t)2 * L.cout * 8;
     std::vector<uint16_t> hi((size_t)L.n_slabs * half);
     for (int k = 0; k < L.n_slabs; ++k)
-      memcpy(&hi[(size_t)k * half], &blob[(size_t)k * 2 * half], half * 2);
+      for (int pl = 0; pl < 2; ++pl)
+        memcpy(&hi[(size_t)k * half + (size_t)pl * L.cout * 8], &blob[(size_t)k * 2 * half + slab_index(L.cout, pl, 0, 0, 0)],
+               (size_t)L.cout * 8 * 2);
     UMT_CUDA_TRY(cudaMalloc(&L.d_weights_hi, hi.size() * 2));
     m->owned.push_back(L.d_weights_hi);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights_hi, hi.data(), hi.size() * 2, cudaMemcpyHostToDevice));
@@ -1211,8 +1243,9 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
       for (int pl = 0; pl < 2; ++pl)
         for (int co = 0; co < L.cout; ++co)
           for (int e = 0; e < 8; ++e) {
-            const size_t src = (size_t)k * 2 * half + ((size_t)pl * L.cout + co) * 8 + e;
-            const float v = bf2f(blob[src]) + bf2f(blob[src + half]);   // hi + lo == the folded fp32 weight (to 2^-17)
+            const size_t src = (size_t)k * 2 * half;
+            const float v = bf2f(blob[src + slab_index(L.cout, pl, 0, co, e)]) +
+                            bf2f(blob[src + slab_index(L.cout, pl, 1, co, e)]);   // hi + lo == the folded fp32 weight (to 2^-17)
             const uint16_t hv = f2h(v);
             h1[(size_t)k * half + ((size_t)pl * L.cout + co) * 8 + e] = hv;
           }
@@ -1425,6 +1458,19 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
     const int force = env_int("UMT_RES_MMA", -1);
     const bool epi = force >= 0 ? force == 0 : (split || L.cout >= 64);
     if (epi) { p.n_stages -= p.res_stages; p.res_epi = 1; }
+  }
+  // tile shape per numeric mode.  The merged split form (issue_taps) keeps two accumulators per sub-tile;
+  // for the 32-channel layers two buffers of S = 2 sub-tiles (epilogue overlapped inside the CTA) beat one
+  // buffer of S = 4 by 28 % (tools/ab_conv.py, B200).  UMT_CONV_SPLIT_CFG<cout>="S,nbuf" overrides.
+  if (split && L.cout <= 112) {
+    int S = (L.cout == 32) ? 2 : p.S, nbuf = 2;
+    const std::string name = "UMT_CONV_SPLIT_CFG" + std::to_string(L.cout);
+    if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d", &S, &nbuf);
+    S = std::max(1, std::min(4, S));
+    while (S > 1 && S * 2 * L.cout * p.occ > 512) S >>= 1;
+    p.S = S;
+    p.patch_rows = S * 128 + p.halo_rows;
+    p.n_buf = (2 * S * 2 * L.cout * p.occ <= 512) ? std::max(1, std::min(2, nbuf)) : 1;
   }
   // pipeline depths from the shared-memory budget
   const int mc = p.S * 128;

@@ -172,7 +172,7 @@ extern "C" void umt_model_destroy(umt_model* m) {
 
 // tail scratch: dense features, three 6x6 planar flat tensors of 144 channels, skeleton maps
 static size_t tail_bytes(int max_images, int max_samples, size_t* feats_off, size_t* a_off,
-                         size_t* b_off, size_t* c_off, size_t* s_off) {
+                         size_t* b_off, size_t* c_off, size_t* s_off, int chunk_images = 0, size_t* u8_off = nullptr) {
   size_t o = 0;
   const size_t flat = align256(flat_tensor_bytes(6, 144, max_samples));
   *feats_off = o; o += align256((size_t)max_images * 72 * 36 * 4);
@@ -180,6 +180,8 @@ static size_t tail_bytes(int max_images, int max_samples, size_t* feats_off, siz
   *b_off = o; o += flat;
   *c_off = o; o += flat;
   *s_off = o; o += align256((size_t)max_samples * 4 * 36 * 4);
+  if (u8_off) *u8_off = o;
+  o += align256((size_t)chunk_images * 9216 * 4);   // float32 staging of one chunk of uint8 crops
   return o;
 }
 
@@ -188,7 +190,7 @@ extern "C" int umt_model_workspace_bytes(const umt_model* m, int chunk_images, i
   if (!m || !bytes || chunk_images < 1 || max_images <= 0 || max_samples <= 0)
     return fail(UMT_ERR_INVALID, "umt_model_workspace_bytes: bad arguments");
   size_t f, a, b, c, s;
-  *bytes = encoder_workspace_bytes(chunk_images) + tail_bytes(max_images, max_samples, &f, &a, &b, &c, &s);
+  *bytes = encoder_workspace_bytes(chunk_images) + tail_bytes(max_images, max_samples, &f, &a, &b, &c, &s, chunk_images);
   return UMT_OK;
 }
 
@@ -209,9 +211,10 @@ extern "C" int umt_model_bind_workspace(umt_model* m, void* workspace, size_t by
   m->ws_max_images = max_images;
   m->ws_max_samples = max_samples;
   encoder_bind(m, m->ws);
-  size_t f, a, b, c, s;
-  tail_bytes(max_images, max_samples, &f, &a, &b, &c, &s);
+  size_t f, a, b, c, s, u8;
+  tail_bytes(max_images, max_samples, &f, &a, &b, &c, &s, chunk_images, &u8);
   uint8_t* t = m->ws + encoder_workspace_bytes(chunk_images);
+  m->img_stage = (float*)(t + u8);
   m->feats = (float*)(t + f);
   m->tail_flat[0] = make_flat_tensor(t + a, 6, 144, max_samples);
   m->tail_flat[1] = make_flat_tensor(t + b, 6, 144, max_samples);
@@ -220,11 +223,35 @@ extern "C" int umt_model_bind_workspace(umt_model* m, void* workspace, size_t by
   return UMT_OK;
 }
 
-static int encode_all(umt_model* m, int mode, const float* images, int n_img, float* features,
-                      cudaStream_t st) {
+// uint8 crop -> float32 in [0,1]: `crop.astype(np.float32) / 255.0` (lib/tracker/tracker.py:211), a true
+// IEEE division like numpy's.  16 pixels per thread.
+__global__ void u8_to_unit_float_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst, long long n16) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n16) return;
+  const uint4 v = __ldg(reinterpret_cast<const uint4*>(src) + i);
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  float4* o = reinterpret_cast<float4*>(dst) + 4 * i;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    o[k] = make_float4(__fdiv_rn((float)(w[k] & 0xFF), 255.0f), __fdiv_rn((float)((w[k] >> 8) & 0xFF), 255.0f),
+                       __fdiv_rn((float)((w[k] >> 16) & 0xFF), 255.0f), __fdiv_rn((float)(w[k] >> 24), 255.0f));
+}
+
+static int encode_all(umt_model* m, int mode, const float* images, const uint8_t* images_u8, int n_img,
+                      float* features, cudaStream_t st) {
   for (int i0 = 0; i0 < n_img; i0 += m->chunk_images) {
     const int n = (n_img - i0 < m->chunk_images) ? n_img - i0 : m->chunk_images;
-    UMT_TRY(encoder_run_chunk(m, mode, images + (size_t)i0 * 9216, n, features + (size_t)i0 * 72 * 36, -1, st));
+    const float* src = images ? images + (size_t)i0 * 9216 : m->img_stage;
+    int extra = 0;
+    if (!images) {
+      const long long n16 = (long long)n * 9216 / 16;
+      u8_to_unit_float_kernel<<<(unsigned)((n16 + 255) / 256), 256, 0, st>>>(images_u8 + (size_t)i0 * 9216, m->img_stage, n16);
+      UMT_TRY(check_launch("u8_to_unit_float_kernel"));
+      extra = 1;
+    }
+    const int before = m->launches;
+    UMT_TRY(encoder_run_chunk(m, mode, src, n, features + (size_t)i0 * 72 * 36, -1, st));
+    m->launches = before + (m->launches - before) + extra;
   }
   return UMT_OK;
 }
@@ -238,10 +265,23 @@ extern "C" int umt_model_encode(umt_model* m, int mode, const float* images, int
   if (n_img < 0) return fail(UMT_ERR_INVALID, "umt_model_encode: n_img=%d", n_img);
   m->launches = 0;
   if (n_img == 0) return UMT_OK;
-  return encode_all(m, mode, images, n_img, features, (cudaStream_t)stream);
+  return encode_all(m, mode, images, nullptr, n_img, features, (cudaStream_t)stream);
 }
 
-extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* images,
+extern "C" int umt_model_encode_u8(umt_model* m, int mode, const uint8_t* images_u8, int n_img, float* features,
+                                   void* stream) {
+  if (!m || !images_u8 || !features) return fail(UMT_ERR_INVALID, "umt_model_encode_u8: null argument");
+  if (mode < UMT_MODE_FP32_EQUIV || mode > UMT_MODE_FP16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
+  if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_encode_u8: no workspace bound");
+  UMT_TRY(check_device(m, "umt_model_encode_u8"));
+  if (((uintptr_t)images_u8 & 15) != 0) return fail(UMT_ERR_INVALID, "umt_model_encode_u8: images must be 16-byte aligned");
+  if (n_img < 0) return fail(UMT_ERR_INVALID, "umt_model_encode_u8: n_img=%d", n_img);
+  m->launches = 0;
+  if (n_img == 0) return UMT_OK;
+  return encode_all(m, mode, nullptr, images_u8, n_img, features, (cudaStream_t)stream);
+}
+
+static int model_forward(umt_model* m, int mode, int head, const float* images, const uint8_t* images_u8,
                                  const float* intrinsics, const float* extrinsics,
                                  const int64_t* sample_range, const int64_t* memory_idx,
                                  const uint8_t* use_memory, const int64_t* hand_idx, int n_img,
@@ -258,9 +298,11 @@ extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* 
   if (n_img <= 0 || n_samples <= 0 || n_img > m->ws_max_images || n_samples > m->ws_max_samples)
     return fail(UMT_ERR_INVALID, "umt_model_forward: n_img=%d n_samples=%d exceed the bound workspace (%d, %d)",
                 n_img, n_samples, m->ws_max_images, m->ws_max_samples);
-  if (!images || !intrinsics || !extrinsics || !sample_range || !memory_idx || !use_memory ||
+  if ((!images && !images_u8) || !intrinsics || !extrinsics || !sample_range || !memory_idx || !use_memory ||
       !hand_idx || !mem_state || !prev_extr || !out_joint_angles || !out_wrist || !out_sigma)
     return fail(UMT_ERR_INVALID, "umt_model_forward: null pointer argument");
+  if (images_u8 && ((uintptr_t)images_u8 & 15) != 0)
+    return fail(UMT_ERR_INVALID, "umt_model_forward_u8: images must be 16-byte aligned");
   if (head == UMT_HEAD_KNOWN_SKELETON) {
     if (!skel_axes || !skel_rest || !(n_skel == 1 || n_skel == n_samples))
       return fail(UMT_ERR_INVALID, "umt_model_forward: known-skeleton head needs 1 or n_samples skeletons");
@@ -270,10 +312,38 @@ extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* 
   if (n_slots <= 0) return fail(UMT_ERR_INVALID, "umt_model_forward: n_slots=%d", n_slots);
   cudaStream_t st = (cudaStream_t)stream;
   m->launches = 0;
-  UMT_TRY(encode_all(m, mode, images, n_img, m->feats, st));
+  UMT_TRY(encode_all(m, mode, images, images_u8, n_img, m->feats, st));
   return tail_forward(m, head, m->feats, intrinsics, extrinsics, sample_range, memory_idx, use_memory,
                       hand_idx, n_img, n_samples, skel_axes, skel_rest, n_skel, mem_state, prev_extr,
                       n_slots, out_joint_angles, out_wrist, out_scale, out_sigma, st);
+}
+
+extern "C" int umt_model_forward(umt_model* m, int mode, int head, const float* images,
+                                 const float* intrinsics, const float* extrinsics,
+                                 const int64_t* sample_range, const int64_t* memory_idx,
+                                 const uint8_t* use_memory, const int64_t* hand_idx, int n_img,
+                                 int n_samples, const float* skel_axes, const float* skel_rest,
+                                 int n_skel, float* mem_state, float* prev_extr, int n_slots,
+                                 float* out_joint_angles, float* out_wrist, float* out_scale,
+                                 float* out_sigma, void* stream) {
+  if (!images) return fail(UMT_ERR_INVALID, "umt_model_forward: null pointer argument");
+  return model_forward(m, mode, head, images, nullptr, intrinsics, extrinsics, sample_range, memory_idx, use_memory,
+                       hand_idx, n_img, n_samples, skel_axes, skel_rest, n_skel, mem_state, prev_extr, n_slots,
+                       out_joint_angles, out_wrist, out_scale, out_sigma, stream);
+}
+
+extern "C" int umt_model_forward_u8(umt_model* m, int mode, int head, const uint8_t* images_u8,
+                                    const float* intrinsics, const float* extrinsics,
+                                    const int64_t* sample_range, const int64_t* memory_idx,
+                                    const uint8_t* use_memory, const int64_t* hand_idx, int n_img,
+                                    int n_samples, const float* skel_axes, const float* skel_rest,
+                                    int n_skel, float* mem_state, float* prev_extr, int n_slots,
+                                    float* out_joint_angles, float* out_wrist, float* out_scale,
+                                    float* out_sigma, void* stream) {
+  if (!images_u8) return fail(UMT_ERR_INVALID, "umt_model_forward_u8: null pointer argument");
+  return model_forward(m, mode, head, nullptr, images_u8, intrinsics, extrinsics, sample_range, memory_idx, use_memory,
+                       hand_idx, n_img, n_samples, skel_axes, skel_rest, n_skel, mem_state, prev_extr, n_slots,
+                       out_joint_angles, out_wrist, out_scale, out_sigma, stream);
 }
 
 // Tools only (not declared in the public header): device buffer [grid][16] of int64 that every

@@ -44,6 +44,7 @@ struct ConvParams {
   int S;                    // 128-row sub-tiles per CTA
   int lo_shift;             // most negative tap shift (rows)
   int patch_rows;           // S*128 + hi_shift - lo_shift
+  int halo_rows;            // hi_shift - lo_shift
   int n_a, n_b;             // pipeline depths (A patches, B slabs)
   int bgroup;               // weight slabs (taps) per B pipeline stage
   int n_buf;                // TMEM accumulator buffers (1 or 2)
@@ -109,6 +110,7 @@ struct umt_model {
   umt::FlatTensor buf[4][3]{};            // per geometry: ping, pong, mid
   umt::FlatTensor phase[4][4]{};          // phase[g]: input of geometry g (g=1..3), 4 parities
   float* feats = nullptr;                 // [max_images,72,36]
+  float* img_stage = nullptr;             // [chunk_images,96,96] float32 staging of uint8 crops
   float* tail_skel = nullptr;             // [max_samples,4,36]
   std::vector<umt::ConvLayer> tail_convs; // fusion(3), temporal(3), regressor_k(4), regressor_u(4)
   umt::FlatTensor tail_flat[3]{};         // 6x6 planar flat scratch, 144 channels capacity

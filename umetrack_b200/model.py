@@ -224,7 +224,10 @@ class UmeTrackModel:
             if images.dim() != 4 or tuple(images.shape[1:]) != (arch.N_IMAGE_FEATURES, arch.FEAT_HW, arch.FEAT_HW):
                 raise ValueError(f"features must be [n,72,6,6], got {tuple(images.shape)}")
         else:
-            images = self._prep(frame_data.left_images, torch.float32)
+            # uint8 crops (as cv2.remap leaves them) are an accepted extension: the `/ 255` of
+            # lib/tracker/tracker.py:211 then runs on the device (umt_model_forward_u8)
+            u8 = frame_data.left_images.dtype == torch.uint8
+            images = self._prep(frame_data.left_images, torch.uint8 if u8 else torch.float32)
             if images.dim() != 3 or tuple(images.shape[1:]) != (arch.CROP_SIZE, arch.CROP_SIZE):
                 raise ValueError(f"left_images must be [n,96,96], got {tuple(images.shape)}")
         intr = self._prep(frame_data.intrinsics, torch.float32)
@@ -271,7 +274,8 @@ class UmeTrackModel:
                     len(self._mem_features), native.ptr(ja), native.ptr(wr), native.ptr(sc), native.ptr(sg),
                     native.current_stream_ptr()), "umt_model_tail")
             else:
-                native.check(lib.umt_model_forward(
+                fwd = lib.umt_model_forward_u8 if images.dtype == torch.uint8 else lib.umt_model_forward
+                native.check(fwd(
                     self._handle, self._mode, head, native.ptr(images), native.ptr(intr), native.ptr(extr),
                     native.ptr(srange), native.ptr(mem_idx), native.ptr(use_mem), native.ptr(hand_idx),
                     n_img, bs, native.ptr(axes), native.ptr(rest), n_skel,
@@ -359,17 +363,19 @@ class UmeTrackModel:
 
     # ---- extras ----------------------------------------------------------------------------
     def encode(self, images: torch.Tensor) -> torch.Tensor:
-        """Backbone only: [n,96,96] -> [n,72,6,6] (the reference's `_image_backbone`)."""
+        """Backbone only: [n,96,96] (float32 in [0,1], or uint8) -> [n,72,6,6] (the reference's
+        `_image_backbone`)."""
         self._require_handle()
-        images = self._prep(images, torch.float32)
+        u8 = images.dtype == torch.uint8
+        images = self._prep(images, torch.uint8 if u8 else torch.float32)
         n = images.shape[0]
         self._ensure_workspace(n, 8)
         out = torch.empty((n, arch.N_IMAGE_FEATURES, arch.FEAT_HW, arch.FEAT_HW), dtype=torch.float32,
                           device=self._device)
         with torch.cuda.device(self._device):
-            native.check(native.lib().umt_model_encode(self._handle, self._mode, native.ptr(images), n,
-                                                       native.ptr(out), native.current_stream_ptr()),
-                         "umt_model_encode")
+            enc = native.lib().umt_model_encode_u8 if u8 else native.lib().umt_model_encode
+            native.check(enc(self._handle, self._mode, native.ptr(images), n, native.ptr(out),
+                             native.current_stream_ptr()), "umt_model_encode")
         self.last_launch_count = native.lib().umt_model_last_launch_count(self._handle)
         return out
 

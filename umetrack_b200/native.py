@@ -38,6 +38,9 @@ SIGNATURES = {
     "umt_model_bind_workspace": (c_int, [c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p]),
     "umt_model_forward": (c_int, [c_void_p, c_int, c_int] + [c_void_p] * 7 + [c_int, c_int, c_void_p,
                                   c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
+    "umt_model_forward_u8": (c_int, [c_void_p, c_int, c_int] + [c_void_p] * 7 + [c_int, c_int, c_void_p,
+                                     c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
+    "umt_model_encode_u8": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "umt_model_tail": (c_int, [c_void_p, c_int] + [c_void_p] * 7 + [c_int, c_int, c_void_p,
                                c_void_p, c_int, c_void_p, c_void_p, c_int] + [c_void_p] * 5),
     "umt_model_tail_scan": (c_int, [c_void_p, c_int] + [c_void_p] * 7 + [c_int, c_void_p, c_void_p, c_int,
