@@ -38,6 +38,7 @@
 
 #include "model.cuh"
 #include "flat.cuh"
+#include "umma.cuh"
 
 namespace umt {
 
@@ -46,149 +47,17 @@ static const int kStageC[4] = {32, 64, 128, 256};
 static const int kStageBlocks[4] = {2, 3, 5, 2};
 
 // ------------------------------------------------------------------------------------------
-// PTX wrappers
-// ------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t done;
-  do {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-  } while (!done);
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes,
-                                         uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
-      : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s_multicast(uint32_t dst, const void* src, uint32_t bytes,
-                                                   uint32_t bar, uint16_t cta_mask) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
-      "[%0], [%1], %2, [%3], %4;"
-      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"(cta_mask)
-      : "memory");
-}
-__device__ __forceinline__ void tc_commit_multicast(uint32_t bar, uint16_t cta_mask) {
-  asm volatile(
-      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-      ::"r"(bar), "h"(cta_mask)
-      : "memory");
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
-}
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred = 0;
-  asm volatile(
-      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
-      "elect.sync rx|px, %1;\n\t"
-      "@px mov.s32 %0, 1;\n\t}"
-      : "+r"(pred)
-      : "r"(0xFFFFFFFFu));
-  return pred != 0;
-}
-__device__ __forceinline__ void tc_fence_before() {
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_fence_after() {
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
-                                            uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t* v) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
-        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
-        "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tc_ld_wait() {
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// UMMA shared-memory descriptor, K-major, SWIZZLE_NONE: start address, LBO (byte distance of
-// the two 8-element K halves), SBO (byte distance of consecutive 8-row groups), version 1.
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) |
-         ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) | (1ull << 46);
-}
-
-// position -> (valid, destination tensor index, destination row)
-struct OutPos {
-  bool valid;
-  int tensor;
-  long long row;
-  long long dense;   // img * H * W + y * W + x (dense NCHW pixel index), for the float32 output mode
-};
-__device__ __forceinline__ OutPos map_output(long long q, int H, int W, int n_pos, int phase_out) {
-  OutPos o;
-  const int Wp = W + 1, S = (H + 1) * Wp;
-  const int img = (int)(q / S);
-  const int rem = (int)(q - (long long)img * S);
-  const int y = rem / Wp, x = rem - y * Wp;
-  o.valid = (q < n_pos) && (x < W) && (y < H);
-  o.dense = ((long long)img * H + y) * W + x;
-  if (!phase_out) {
-    o.tensor = 0;
-    o.row = q;
-  } else {
-    const int W2p = (W >> 1) + 1, S2 = ((H >> 1) + 1) * W2p;
-    o.tensor = ((y & 1) << 1) | (x & 1);
-    o.row = (long long)img * S2 + (y >> 1) * W2p + (x >> 1);
-  }
-  return o;
-}
-
-// ------------------------------------------------------------------------------------------
 // The implicit-GEMM convolution kernel
 // ------------------------------------------------------------------------------------------
 constexpr int kConvThreads = 256;   // 4 control warps + 4 epilogue warps
 
-__device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) {
-  return ((uint64_t)hi << 32) | (uint64_t)lo;
-}
 
 // Issue the MMAs of `n` consecutive taps (one weight stage) for all S sub-tiles.  Descriptors are
 // advanced by adding to their low word: +shift rows for a tap, +128 (2048 B) per sub-tile, +slab
 // bytes per tap on the weight side; everything else is loop invariant.
 // Split mode, weight slab = [plane 0: hi rows, lo rows][plane 1: hi rows, lo rows], so the hi rows alone
 // (N = COUT) and hi|lo together (N = 2 COUT) are the same descriptor with a different N.
-//   MERGE (COUT <= 112): two MMAs per tap and sub-tile instead of three:
+//   MERGE (COUT <= 64): two MMAs per tap and sub-tile instead of three:
 //       [D1 | D2] += a_hi * [w_hi | w_lo]   (N = 2 COUT)        D1 += a_lo * w_hi   (N = COUT)
 //   and the epilogue adds D1 + D2.  The narrow layers are bound by the shared-memory operand path
 //   (every MMA re-reads its 4 KB A tile), so one A read fewer per tap is 27 % fewer operand bytes.
@@ -243,12 +112,11 @@ __device__ __forceinline__ void issue_taps(const ConvParams& P, int stage, int t
 // EPI selects the epilogue (kept out of the loop body at compile time: the epilogue warps run one
 // warp per scheduler, so every instruction they fetch is on the path that frees the accumulator):
 // 0 = bias/ReLU -> planar rows, 1 = + identity residual, 2 = float32 NCHW output (projection).
-constexpr int kEpiPlain = 0, kEpiResidual = 1, kEpiDense = 2;
 template <int COUT, int MODE, int EPI>
 __global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma_kernel(const __grid_constant__ ConvParams P) {
   constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
-  constexpr bool MERGE = SPLIT && COUT <= 112;              // see issue_taps
+  constexpr bool MERGE = SPLIT && COUT <= 64;               // see issue_taps (backbone widths 32 and 64)
   constexpr int kDCols = MERGE ? 2 * COUT : COUT;           // accumulator columns per sub-tile
   extern __shared__ __align__(128) uint8_t smem[];
   // [0,1024): barriers + tmem pointer; [1024, 1024+COUT*4): bias; then A stages, then B stages
@@ -621,6 +489,7 @@ static int launch_conv_c(const ConvParams& p, int mode, cudaStream_t st) {
 }
 
 int launch_conv(const ConvParams& p, int cout, int mode, cudaStream_t st) {
+  if (p.pair_weights) return launch_conv_pair(p, cout, mode, st);   // 128 / 256 channels: CTA pairs (conv_pair.cu)
   switch (cout) {
     case 32: return launch_conv_c<32>(p, mode, st);
     case 64: return launch_conv_c<64>(p, mode, st);
@@ -1253,6 +1122,20 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     m->owned.push_back(L.d_weights_h16);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights_h16, h1.data(), h1.size() * 2, cudaMemcpyHostToDevice));
   }
+  if (main.ks == 3 && L.stride == 1 && p.a_nsrc == 1 && (L.cout == 128 || L.cout == 256)) {
+    // weights repacked per CTA half for the pair kernel (conv_pair.cu); the trailing identity stages are
+    // not part of it (these widths always add the residual in the epilogue)
+    std::vector<int> ntaps;
+    for (int i = 0; i < ns - p.res_stages; ++i) ntaps.push_back(p.st_ntaps[i]);
+    for (int kind = 0; kind < 3; ++kind) {
+      L.pair_G[kind] = (kind == 0 || L.cout == 256) ? 3 : 9;
+      std::vector<uint16_t> pb;
+      pack_pair_blob(blob, L.cout, ntaps, L.pair_G[kind], kind, f2h, bf2f, pb);
+      UMT_CUDA_TRY(cudaMalloc(&L.d_pair[kind], pb.size() * 2));
+      m->owned.push_back(L.d_pair[kind]);
+      UMT_CUDA_TRY(cudaMemcpy(L.d_pair[kind], pb.data(), pb.size() * 2, cudaMemcpyHostToDevice));
+    }
+  }
   if (main.ks == 3 && L.stride == 2 && env_int("UMT_CONV_S2_MERGE", 2) == 2) {
     // the 16-bit modes have the shared memory for all four phase patches in one stage
     L.prog16 = p;
@@ -1459,10 +1342,17 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
     const bool epi = force >= 0 ? force == 0 : (split || L.cout >= 64);
     if (epi) { p.n_stages -= p.res_stages; p.res_epi = 1; }
   }
+  // 128 / 256 channels, stride 1: the CTA-pair kernel (UMT_CONV_PAIR=0 falls back to one CTA per tile)
+  p.pair_weights = nullptr;
+  if (L.d_pair[0] && pair_kernel_enabled() && !p.dense_out && (p.res_stages == 0 || p.res_epi)) {
+    const int kind = split ? 0 : (mode == UMT_MODE_FP16 ? 2 : 1);
+    p.pair_weights = L.d_pair[kind];
+    p.pair_G = L.pair_G[kind];
+  }
   // tile shape per numeric mode.  The merged split form (issue_taps) keeps two accumulators per sub-tile;
   // for the 32-channel layers two buffers of S = 2 sub-tiles (epilogue overlapped inside the CTA) beat one
   // buffer of S = 4 by 28 % (tools/ab_conv.py, B200).  UMT_CONV_SPLIT_CFG<cout>="S,nbuf" overrides.
-  if (split && L.cout <= 112) {
+  if (split && L.cout <= 64) {
     int S = (L.cout == 32) ? 2 : p.S, nbuf = 2;
     const std::string name = "UMT_CONV_SPLIT_CFG" + std::to_string(L.cout);
     if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d", &S, &nbuf);

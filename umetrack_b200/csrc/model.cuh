@@ -35,6 +35,8 @@ struct ConvParams {
   FlatTensor src[5];
   FlatTensor out[4];        // [0] for flat output; four parity-phase tensors when phase_out
   const uint8_t* weights;   // packed operand slabs in program order
+  const uint8_t* pair_weights;   // non-null: run through the CTA-pair kernel (conv_pair.cu) with this blob
+  int pair_G;                    // taps per weight stage of that blob
   float* dense_out;         // if set: write float32 NCHW [n, dense_c, H, W] instead of the planar layout
   int dense_c;
   long long* dbg;           // optional [grid][16] cycle counters (tools/conv_timeline.py); nullptr in production
@@ -75,6 +77,8 @@ struct ConvLayer {
   uint8_t* d_weights = nullptr;                   // packed [slab][hi|lo][2][cout][8] bf16
   uint8_t* d_weights_hi = nullptr;                // packed [slab][2][cout][8] bf16 (hi only)
   uint8_t* d_weights_h16 = nullptr;               // fp16 weights, one-CTA packing [slab][2][cout][8]
+  uint8_t* d_pair[3] = {nullptr, nullptr, nullptr};   // pair-kernel blobs: split bf16, bf16, fp16 (conv_pair.cu)
+  int pair_G[3] = {0, 0, 0};
   float* d_bias = nullptr;
   ConvParams prog{};                              // program template (tensors filled per call)
   ConvParams prog16{};                            // stride-2 layers: stage table used by the 16-bit modes
@@ -136,6 +140,11 @@ int launch_conv(const ConvParams& p, int cout, int mode, cudaStream_t st);
 void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode);
 size_t flat_tensor_bytes(int H, int C, int n_img);
 FlatTensor make_flat_tensor(uint8_t* base, int H, int C, int n_img);
+// conv_pair.cu
+int launch_conv_pair(const ConvParams& p, int cout, int mode, cudaStream_t st);
+int pair_kernel_enabled();
+void pack_pair_blob(const std::vector<uint16_t>& blob, int cout, const std::vector<int>& stage_ntaps, int G, int kind,
+                    uint16_t (*to_half)(float), float (*from_bf)(uint16_t), std::vector<uint16_t>& out);
 // tail.cu
 int tail_build(umt_model* m, const float* const* t);
 int tail_forward(umt_model* m, int head, const float* feats, const float* intrinsics,
