@@ -48,9 +48,11 @@ struct alignas(64) PairParams {
   const float* bias;
   unsigned* status;
   int H, W, n_pos;
-  int n_tiles;              // pair tiles of 256 positions
+  int n_tiles;              // pair tiles of 2 * S * 128 positions
   int n_a, n_b, n_buf, G;
-  int lo_shift, patch_rows;
+  int S;                    // 128-row sub-tiles per CTA (each MMA covers sub-tile s of both CTAs)
+  int box_rows, n_box;      // an A plane arrives as n_box TMA boxes of box_rows rows (box limit: 256 rows)
+  int lo_shift, patch_rows; // patch_rows = n_box * box_rows >= S*128 + halo: rows of one plane in shared memory
   int guard[2], planes[2];  // guard rows / hi planes (C/8) of the two sources
   int n_stages;
   int relu, res_epi, phase_out;
@@ -97,13 +99,19 @@ __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
 }
 
 // EPI: 0 = bias/ReLU -> planar rows, 1 = + identity residual (same meaning as in encoder.cu)
-template <int COUT, int MODE, int EPI>
+template <int COUT, int MODE, int EPI, int S>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 2)
 conv_pair_kernel(const __grid_constant__ PairParams P) {
   constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
-  constexpr int kHalf = COUT / 2;                                  // weight rows held by one CTA
-  constexpr uint32_t kBPart = (uint32_t)kHalf * 16u;               // one of {hi, lo} of one plane
-  constexpr uint32_t kBPlane = (SPLIT ? 2u : 1u) * kBPart;         // plane distance (descriptor LBO)
+  // Narrow layers in the split mode use the merged form of encoder.cu's issue_taps: per tap
+  //   [D1 | D2] += a_hi * [w_hi | w_lo]  (N = 2 COUT)      D1 += a_lo * w_hi  (N = COUT)
+  // A pair splits the N rows of B between its CTAs, so for the first MMA CTA 0 holds all hi rows and CTA 1
+  // all lo rows (region X, COUT rows), and for the second each holds its half of the hi rows (region Y).
+  constexpr bool MERGE = SPLIT && COUT <= 64;
+  constexpr int kDCols = MERGE ? 2 * COUT : COUT;                  // accumulator columns per buffer
+  constexpr int kHalf = COUT / 2;                                  // weight rows of one CTA for an N = COUT MMA
+  constexpr uint32_t kBPart = (uint32_t)kHalf * 16u;               // one of {hi, lo} of one plane (plain form)
+  constexpr uint32_t kBPlane = MERGE ? 3u * kBPart : (SPLIT ? 2u : 1u) * kBPart;   // plane distance (descriptor LBO)
   constexpr uint32_t kBTap = 2u * kBPlane;                         // bytes of one tap in one CTA
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -131,7 +139,8 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
   const bool leader_cta = rank == 0;
   const int n_pairs = (int)(gridDim.x >> 1), pair_id = (int)(blockIdx.x >> 1);
-  const uint32_t want_cols = (uint32_t)(COUT * n_buf);
+  constexpr uint32_t buf_cols = (uint32_t)(S * kDCols);
+  const uint32_t want_cols = buf_cols * (uint32_t)n_buf;
   const uint32_t tmem_cols = want_cols <= 32u ? 32u : want_cols <= 64u ? 64u : want_cols <= 128u ? 128u
                              : want_cols <= 256u ? 256u : 512u;
 
@@ -161,7 +170,7 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
     // ===== A-patch producer (both CTAs): own 128 positions + halo, one 16-channel slice per stage =====
     int it = 0;
     for (int tile = pair_id; tile < P.n_tiles; tile += n_pairs) {
-      const long long q0 = (long long)tile * 256 + (long long)rank * 128;
+      const long long q0 = ((long long)tile * 2 + rank) * (S * 128);
       for (int i = 0; i < P.n_stages; ++i, ++it) {
         const int slot = it % n_a;
         mbar_wait(a_empty(slot), ((uint32_t)(it / n_a) & 1u) ^ 1u);
@@ -170,8 +179,19 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
         const int row = (int)(P.guard[src] + q0 + P.lo_shift);
         const uint32_t dst = smem_u32(a_base + (size_t)slot * a_stage_stride);
         const uint32_t bar = a_full(slot) & kPeerBitMask;
-        tma_load_3d_pair(dst, &P.mapA[src], 0, row, 2 * P.st_chunk[i], bar);
-        if (SPLIT) tma_load_3d_pair(dst + 2 * a_plane_bytes, &P.mapA[src], 0, row, P.planes[src] + 2 * P.st_chunk[i], bar);
+        const uint32_t box_bytes = (uint32_t)P.box_rows * 16u;
+        // shared-memory planes: hi plane 0, hi plane 1 [, lo plane 0, lo plane 1]; each in n_box boxes
+        if (P.n_box == 1) {   // the box covers both planes of the slice
+          tma_load_3d_pair(dst, &P.mapA[src], 0, row, 2 * P.st_chunk[i], bar);
+          if (SPLIT) tma_load_3d_pair(dst + 2 * a_plane_bytes, &P.mapA[src], 0, row, P.planes[src] + 2 * P.st_chunk[i], bar);
+        } else {
+          for (int pl = 0; pl < (SPLIT ? 4 : 2); ++pl) {
+            const int gplane = (pl >> 1) * P.planes[src] + 2 * P.st_chunk[i] + (pl & 1);
+            for (int bx = 0; bx < P.n_box; ++bx)
+              tma_load_3d_pair(dst + (uint32_t)pl * a_plane_bytes + (uint32_t)bx * box_bytes, &P.mapA[src], 0,
+                               row + bx * P.box_rows, gplane, bar);
+          }
+        }
       }
     }
   } else if (warp == 1 && lane == 0) {
@@ -210,7 +230,7 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
       const int buf = tc % n_buf;
       mbar_wait(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // both CTAs' epilogues drained this buffer
       tc_fence_after();
-      const uint32_t d = tmem_base + (uint32_t)buf * (uint32_t)COUT;
+      const uint32_t d0 = tmem_base + (uint32_t)buf * buf_cols;
       uint32_t any = 0;
       for (int i = 0; i < P.n_stages; ++i, ++it) {
         const int aslot = it % n_a;
@@ -228,15 +248,28 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
           if (leader) {
 #pragma unroll 1
             for (int j = 0; j < n; ++j) {
-              const uint32_t a0 = a_lo32 + (uint32_t)((int)P.tap_shift[tap0 + t0 + j] - P.lo_shift);
-              const uint64_t a_hi = desc64(a0, a_hi32);
+              const uint32_t a00 = a_lo32 + (uint32_t)((int)P.tap_shift[tap0 + t0 + j] - P.lo_shift);
               const uint64_t b_hi = desc64(b_lo32 + (uint32_t)j * (kBTap >> 4), b_hi32);
-              tc_mma_pair(d, a_hi, b_hi, idesc, any);
-              if (SPLIT) {
+#pragma unroll
+              for (int sb = 0; sb < S; ++sb) {
+              const uint32_t a0 = a00 + (uint32_t)sb * 128u;
+              const uint32_t d = d0 + (uint32_t)sb * (uint32_t)kDCols;
+              const uint64_t a_hi = desc64(a0, a_hi32);
+              if (MERGE) {
+                constexpr uint32_t idesc_wide = (idesc & ~(0x3Fu << 17)) | ((uint32_t)((2 * COUT) >> 3) << 17);
                 const uint64_t a_lo = desc64(a0 + a_lo_plane16, a_hi32);
-                const uint64_t b_lo = desc64(b_lo32 + (uint32_t)j * (kBTap >> 4) + (kBPart >> 4), b_hi32);
-                tc_mma_pair(d, a_hi, b_lo, idesc, 1u);
-                tc_mma_pair(d, a_lo, b_hi, idesc, 1u);
+                const uint64_t b_y = desc64(b_lo32 + (uint32_t)j * (kBTap >> 4) + ((2u * kBPart) >> 4), b_hi32);
+                tc_mma_pair(d, a_hi, b_hi, idesc_wide, any);   // region X: [w_hi | w_lo] over the pair
+                tc_mma_pair(d, a_lo, b_y, idesc, 1u);          // region Y: w_hi halves
+              } else {
+                tc_mma_pair(d, a_hi, b_hi, idesc, any);
+                if (SPLIT) {
+                  const uint64_t a_lo = desc64(a0 + a_lo_plane16, a_hi32);
+                  const uint64_t b_lo = desc64(b_lo32 + (uint32_t)j * (kBTap >> 4) + (kBPart >> 4), b_hi32);
+                  tc_mma_pair(d, a_hi, b_lo, idesc, 1u);
+                  tc_mma_pair(d, a_lo, b_hi, idesc, 1u);
+                }
+              }
               }
               any = 1u;
             }
@@ -255,10 +288,11 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
     // ===== epilogue (both CTAs): own 128 rows of the accumulator -> bias / residual / ReLU -> global =====
     const int lgrp = warp & 3;
     int tc = 0;
-    constexpr int kStep = 32, kRows = kStep / 8;
+    constexpr int kStep = MERGE ? 16 : 32, kRows = kStep / 8;
     for (int tile = pair_id; tile < P.n_tiles; tile += n_pairs, ++tc) {
       const int buf = tc % n_buf;
-      const long long q = (long long)tile * 256 + (long long)rank * 128 + lgrp * 32 + lane;
+      for (int sb = 0; sb < S; ++sb) {
+      const long long q = ((long long)tile * 2 + rank) * (S * 128) + sb * 128 + lgrp * 32 + lane;
       const OutPos o = map_output(q, P.H, P.W, P.n_pos, P.phase_out);
       uint4 rn_h[kRows], rn_l[kRows];
       auto res_fetch = [&](int c0) {
@@ -282,16 +316,21 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
           }
         }
       }
-      mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
-      tc_fence_after();
+      if (sb == 0) {
+        mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
+        tc_fence_after();
+      }
       const FlatTensor& T = P.out[o.tensor];
       const float lo_clamp = P.relu ? 0.0f : -INFINITY;
 #pragma unroll 1
       for (int c0 = 0; c0 < COUT; c0 += kStep) {
         uint32_t v[kStep];
-        const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)buf * (uint32_t)COUT + (uint32_t)c0;
+        uint32_t v2[MERGE ? kStep : 1];   // D2 = a_hi * w_lo of the merged form
+        const uint32_t taddr = tmem_base + ((uint32_t)(lgrp * 32) << 16) + (uint32_t)buf * buf_cols +
+                               (uint32_t)(sb * kDCols + c0);
         tc_ld16(taddr, v);
-        tc_ld16(taddr + 16, v + 16);
+        if (kStep == 32) tc_ld16(taddr + 16, v + 16);
+        if (MERGE) tc_ld16(taddr + COUT, v2);
         uint4 rc_h[kRows], rc_l[kRows];
         if (EPI == kEpiResidual) {
 #pragma unroll
@@ -304,7 +343,11 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
           for (int h = 0; h < kRows; ++h) {
             float f[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[h * 8 + e]) + s_bias[c0 + h * 8 + e];
+            for (int e = 0; e < 8; ++e) {
+              f[e] = __uint_as_float(v[h * 8 + e]);
+              if (MERGE) f[e] += __uint_as_float(v2[h * 8 + e]);
+              f[e] += s_bias[c0 + h * 8 + e];
+            }
             if (EPI == kEpiResidual) {
               float r[8];
               decode_row8<MODE>(rc_h[h], rc_l[h], r);
@@ -316,6 +359,7 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
             store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
           }
         }
+      }
       }
       tc_fence_before();
       __syncwarp();
@@ -364,11 +408,11 @@ static int make_map(CUtensorMap* m, int rank, void* base, const cuuint64_t* dims
 }
 
 // 3-D view of an activation tensor: {8 channels of a row, rows of a plane, planes (hi then lo)}
-static int make_map_a(CUtensorMap* m, const FlatTensor& T, int patch_rows) {
+static int make_map_a(CUtensorMap* m, const FlatTensor& T, int box_rows, int box_planes) {
   const cuuint64_t planes = (cuuint64_t)(2 * (T.lo_offset / T.plane_stride));
   const cuuint64_t dims[3] = {8, (cuuint64_t)(T.plane_stride / 16), planes};
   const cuuint64_t strides[2] = {16, (cuuint64_t)T.plane_stride};
-  const cuuint32_t box[3] = {8, (cuuint32_t)patch_rows, 2};
+  const cuuint32_t box[3] = {8, (cuuint32_t)box_rows, (cuuint32_t)box_planes};
   return make_map(m, 3, T.base, dims, strides, box);
 }
 
@@ -379,10 +423,16 @@ static int make_map_b(CUtensorMap* m, const uint8_t* blob, size_t bytes, int box
   return make_map(m, 2, const_cast<uint8_t*>(blob), dims, strides, box);
 }
 
+// bytes of one tap in one CTA (see the kernel's kBTap)
+static size_t pair_tap_bytes(int cout, bool split) {
+  const size_t part = (size_t)(cout / 2) * 16;
+  return 2 * ((split && cout <= 64) ? 3 * part : (split ? 2 : 1) * part);
+}
+
 static size_t pair_smem_bytes(const PairParams& p, int cout, bool split) {
   const size_t bias = ((size_t)cout * 4 + 127) / 128 * 128;
   const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
-  const size_t b = (size_t)p.G * (cout / 2) * 16 * 2 * (split ? 2 : 1);
+  const size_t b = (size_t)p.G * pair_tap_bytes(cout, split);
   return 1024 + bias + a * p.n_a + b * p.n_b;
 }
 
@@ -396,19 +446,46 @@ static int pair_sm_count() {
   return n;
 }
 
-template <int COUT, int MODE>
-static int launch_pair_t(const PairParams& p, cudaStream_t st) {
+template <int COUT, int MODE, int S>
+static int launch_pair_s(const PairParams& p, cudaStream_t st) {
   const size_t smem = pair_smem_bytes(p, COUT, MODE == UMT_MODE_FP32_EQUIV);
-  void (*kernel)(PairParams) = p.res_epi ? conv_pair_kernel<COUT, MODE, kEpiResidual> : conv_pair_kernel<COUT, MODE, kEpiPlain>;
+  void (*kernel)(PairParams) = p.res_epi ? conv_pair_kernel<COUT, MODE, kEpiResidual, S> : conv_pair_kernel<COUT, MODE, kEpiPlain, S>;
   UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int pairs = std::max(1, std::min(p.n_tiles, pair_sm_count()));   // two CTAs per SM = one pair per SM on average
   kernel<<<2 * pairs, kPairThreads, smem, st>>>(p);
   return check_launch("conv_pair_kernel");
 }
 
-int pair_kernel_enabled() {
-  const char* e = getenv("UMT_CONV_PAIR");   // read per launch so that tools can alternate (tools/ab_conv.py)
-  return e ? atoi(e) : 1;
+// UMT_CONV_PAIR: 0 = never, 1 = default selection, "32,64,..." = exactly these widths (all modes).
+// Read per launch so that tools can alternate (tools/ab_conv.py).
+// sub-tiles per CTA that exist as kernels: accumulators of S sub-tiles must fit 256 TMEM columns
+template <int COUT, int MODE>
+static int launch_pair_t(const PairParams& p, cudaStream_t st) {
+  constexpr int kDCols = (MODE == UMT_MODE_FP32_EQUIV && COUT <= 64) ? 2 * COUT : COUT;
+  if (p.S == 1) return launch_pair_s<COUT, MODE, 1>(p, st);
+  if constexpr (2 * kDCols <= 256) {
+    if (p.S == 2) return launch_pair_s<COUT, MODE, 2>(p, st);
+  }
+  if constexpr (4 * kDCols <= 256) {
+    if (p.S == 4) return launch_pair_s<COUT, MODE, 4>(p, st);
+  }
+  return fail(UMT_ERR_INVALID, "pair conv: S = %d not available for Cout %d", p.S, COUT);
+}
+
+int pair_kernel_enabled(int cout, int mode) {
+  const char* e = getenv("UMT_CONV_PAIR");
+  // default (B200, tools/ab_conv.py): pairs win for 128 / 256 channels in every mode (+14 % / +8 % in the
+  // 16-bit modes, +17 % / +4 % in the split mode) and for 64 channels in the split mode (+8 %); the
+  // 32-channel layers (and 64 channels in the 16-bit modes) are faster with one CTA per tile, whose
+  // four sub-tiles per CTA keep the halo of the 48x48 raster at 20 % of the A traffic
+  if (!e || !strcmp(e, "1")) return cout >= 128 || (cout == 64 && mode == UMT_MODE_FP32_EQUIV);
+  if (!strcmp(e, "0")) return 0;
+  if (!strcmp(e, "all")) return 1;
+  char key[16];
+  snprintf(key, sizeof key, "%d", cout);
+  for (const char* q = e; (q = strstr(q, key)); q += strlen(key))
+    if ((q == e || q[-1] == ',') && (q[strlen(key)] == ',' || q[strlen(key)] == 0)) return 1;
+  return 0;
 }
 
 // Launch one eligible convolution (see finalize_conv_params) through the pair kernel.
@@ -417,10 +494,31 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
   PairParams p;
   memset(&p, 0, sizeof(p));
   p.H = c.H; p.W = c.W; p.n_pos = c.n_pos;
-  p.n_tiles = (c.n_pos + 255) / 256;
+  // sub-tiles per CTA: the halo of a 128-row tile is 78 % extra A traffic at 48x48 and 41 % at 24x24, so the
+  // wide-raster layers take more rows per CTA (UMT_PAIR_S<cout> overrides)
+  const int dcols = (split && cout <= 64) ? 2 * cout : cout;
+  int S = (cout == 32) ? (split ? 2 : 4) : (cout == 64 && !split) ? 2 : 1;
+  {
+    const std::string name = "UMT_PAIR_S" + std::to_string(cout);
+    if (const char* e = getenv(name.c_str())) S = atoi(e);
+  }
+  S = (S >= 4) ? 4 : (S >= 2) ? 2 : 1;
+  while (S > 1 && S * dcols > 256) S >>= 1;
+  p.S = S;
+  p.n_tiles = (c.n_pos + 256 * S - 1) / (256 * S);
   p.G = c.pair_G;
   p.lo_shift = c.lo_shift;
-  p.patch_rows = 128 + c.halo_rows;
+  const int need_rows = S * 128 + c.halo_rows;
+  p.n_box = (need_rows + 255) / 256;
+  p.box_rows = ((need_rows + p.n_box - 1) / p.n_box + 7) / 8 * 8;   // multiple of 8 rows: 128-byte aligned box destinations
+  if (p.n_box == 1) {
+    // one two-plane box: only the box itself must be 128-byte aligned (rows % 4 == 0).  Keep the plane
+    // distance at 64 mod 128 bytes: with a multiple of 128 the two K halves of the A operand start in the
+    // same banks and the MMA's operand fetch slows down (measured -20 % on the 128-channel layers)
+    p.box_rows = (need_rows + 3) / 4 * 4;
+    if (p.box_rows % 8 == 0 && !getenv("UMT_PAIR_NO_SKEW")) p.box_rows += 4;
+  }
+  p.patch_rows = p.n_box * p.box_rows;
   p.relu = c.relu; p.res_epi = c.res_epi; p.phase_out = c.phase_out;
   p.bias = c.bias;
   p.res = c.res;
@@ -429,23 +527,23 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
   p.n_stages = c.n_stages;
   int n_taps_total = 0;
   for (int i = 0; i < c.n_stages; ++i) {
-    if (c.st_src[i] > 1) return fail(UMT_ERR_INVALID, "pair conv: source %d", (int)c.st_src[i]);
+    if (c.st_src[i] > 1 || c.tap_src[c.st_tap0[i]] != 0) return fail(UMT_ERR_INVALID, "pair conv: source %d", (int)c.st_src[i]);
     if (!(c.st_ntaps[i] == 1 || c.st_ntaps[i] % p.G == 0))
       return fail(UMT_ERR_INVALID, "pair conv: %d taps per stage with groups of %d", (int)c.st_ntaps[i], p.G);
     p.st_src[i] = c.st_src[i]; p.st_chunk[i] = c.st_chunk[i]; p.st_ntaps[i] = c.st_ntaps[i]; p.st_tap0[i] = c.st_tap0[i];
     n_taps_total += c.st_ntaps[i];
   }
   for (int t = 0; t < kMaxTaps; ++t) p.tap_shift[t] = c.tap_shift[t];
-  if (p.patch_rows > 256) return fail(UMT_ERR_INVALID, "pair conv: patch of %d rows exceeds the TMA box limit", p.patch_rows);
+  if (p.box_rows > 256) return fail(UMT_ERR_INVALID, "pair conv: box of %d rows exceeds the TMA limit", p.box_rows);
   // tensor maps (host-side encode, a few hundred nanoseconds each)
-  const size_t tap_bytes = (size_t)(cout / 2) * 16 * 2 * (split ? 2 : 1);
+  const size_t tap_bytes = pair_tap_bytes(cout, split);
   const size_t blob_bytes = (size_t)n_taps_total * 2 * tap_bytes;
   for (int s = 0; s < 2; ++s) {
     const FlatTensor& T = c.src[s];
     if (!T.base) continue;
     p.guard[s] = T.guard;
     p.planes[s] = (int)(T.lo_offset / T.plane_stride);
-    UMT_TRY(make_map_a(&p.mapA[s], T, p.patch_rows));
+    UMT_TRY(make_map_a(&p.mapA[s], T, p.box_rows, p.n_box == 1 ? 2 : 1));
   }
   UMT_TRY(make_map_b(&p.mapB[0], c.pair_weights, blob_bytes, (int)(p.G * tap_bytes / 256)));
   UMT_TRY(make_map_b(&p.mapB[1], c.pair_weights, blob_bytes, (int)(tap_bytes / 256)));
@@ -454,14 +552,21 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
   const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   const size_t fixed = 1024 + ((size_t)cout * 4 + 127) / 128 * 128;
   const size_t b = (size_t)p.G * tap_bytes;
-  int n_a = 4;
+  int n_a = (cout <= 64) ? 6 : 4;
+  if (const char* e = getenv("UMT_PAIR_NA")) n_a = std::max(2, atoi(e));
   while (n_a > 2 && fixed + a * n_a + b * 2 > budget) --n_a;
   long long nb = ((long long)budget - (long long)fixed - (long long)(a * n_a)) / (long long)b;
   if (nb < 2) return fail(UMT_ERR_INVALID, "pair conv: weight stages do not fit");
   p.n_a = n_a;
   p.n_b = (int)std::min(12LL, nb);
-  p.n_buf = (2 * cout <= 256) ? 2 : 1;
+  p.n_buf = (2 * S * dcols <= 256) ? 2 : 1;
   switch (cout * 4 + mode) {
+    case 32 * 4 + UMT_MODE_FP32_EQUIV: return launch_pair_t<32, UMT_MODE_FP32_EQUIV>(p, st);
+    case 32 * 4 + UMT_MODE_BF16: return launch_pair_t<32, UMT_MODE_BF16>(p, st);
+    case 32 * 4 + UMT_MODE_FP16: return launch_pair_t<32, UMT_MODE_FP16>(p, st);
+    case 64 * 4 + UMT_MODE_FP32_EQUIV: return launch_pair_t<64, UMT_MODE_FP32_EQUIV>(p, st);
+    case 64 * 4 + UMT_MODE_BF16: return launch_pair_t<64, UMT_MODE_BF16>(p, st);
+    case 64 * 4 + UMT_MODE_FP16: return launch_pair_t<64, UMT_MODE_FP16>(p, st);
     case 128 * 4 + UMT_MODE_FP32_EQUIV: return launch_pair_t<128, UMT_MODE_FP32_EQUIV>(p, st);
     case 128 * 4 + UMT_MODE_BF16: return launch_pair_t<128, UMT_MODE_BF16>(p, st);
     case 128 * 4 + UMT_MODE_FP16: return launch_pair_t<128, UMT_MODE_FP16>(p, st);
@@ -479,6 +584,7 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
 void pack_pair_blob(const std::vector<uint16_t>& blob, int cout, const std::vector<int>& stage_ntaps, int G, int kind,
                     uint16_t (*to_half)(float), float (*from_bf)(uint16_t), std::vector<uint16_t>& out) {
   const int parts = (kind == 0) ? 2 : 1, half = cout / 2;
+  const bool merge = (kind == 0 && cout <= 64);   // [plane][X: all hi rows (CTA 0) / all lo rows (CTA 1)][Y: own half of the hi rows]
   const size_t slab = (size_t)4 * cout * 8;
   out.clear();
   int k = 0;
@@ -488,6 +594,15 @@ void pack_pair_blob(const std::vector<uint16_t>& blob, int cout, const std::vect
       for (int r = 0; r < 2; ++r)
         for (int j = 0; j < n; ++j) {
           const uint16_t* s = &blob[(size_t)(k + j) * slab];
+          if (merge) {
+            for (int pl = 0; pl < 2; ++pl) {
+              for (int co = 0; co < cout; ++co)
+                for (int e = 0; e < 8; ++e) out.push_back(s[(((size_t)pl * 2 + r) * cout + co) * 8 + e]);
+              for (int co = r * half; co < (r + 1) * half; ++co)
+                for (int e = 0; e < 8; ++e) out.push_back(s[(((size_t)pl * 2 + 0) * cout + co) * 8 + e]);
+            }
+            continue;
+          }
           for (int pl = 0; pl < 2; ++pl)
             for (int part = 0; part < parts; ++part)
               for (int co = r * half; co < (r + 1) * half; ++co)

@@ -1122,13 +1122,14 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     m->owned.push_back(L.d_weights_h16);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights_h16, h1.data(), h1.size() * 2, cudaMemcpyHostToDevice));
   }
-  if (main.ks == 3 && L.stride == 1 && p.a_nsrc == 1 && (L.cout == 128 || L.cout == 256)) {
+  if (main.ks == 3 && L.stride == 1 && p.a_nsrc == 1 && (L.cout == 32 || L.cout == 64 || L.cout == 128 || L.cout == 256)) {
     // weights repacked per CTA half for the pair kernel (conv_pair.cu); the trailing identity stages are
     // not part of it (these widths always add the residual in the epilogue)
     std::vector<int> ntaps;
     for (int i = 0; i < ns - p.res_stages; ++i) ntaps.push_back(p.st_ntaps[i]);
     for (int kind = 0; kind < 3; ++kind) {
       L.pair_G[kind] = (kind == 0 || L.cout == 256) ? 3 : 9;
+      if (const char* e = getenv(kind == 0 ? "UMT_PAIR_G_SPLIT" : "UMT_PAIR_G16")) { const int g = atoi(e); if (g == 1 || g == 3 || g == 9) L.pair_G[kind] = g; }
       std::vector<uint16_t> pb;
       pack_pair_blob(blob, L.cout, ntaps, L.pair_G[kind], kind, f2h, bf2f, pb);
       UMT_CUDA_TRY(cudaMalloc(&L.d_pair[kind], pb.size() * 2));
@@ -1344,7 +1345,7 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   }
   // 128 / 256 channels, stride 1: the CTA-pair kernel (UMT_CONV_PAIR=0 falls back to one CTA per tile)
   p.pair_weights = nullptr;
-  if (L.d_pair[0] && pair_kernel_enabled() && !p.dense_out && (p.res_stages == 0 || p.res_epi)) {
+  if (L.d_pair[0] && pair_kernel_enabled(L.cout, mode) && !p.dense_out && (p.res_stages == 0 || p.res_epi)) {
     const int kind = split ? 0 : (mode == UMT_MODE_FP16 ? 2 : 1);
     p.pair_weights = L.d_pair[kind];
     p.pair_G = L.pair_G[kind];

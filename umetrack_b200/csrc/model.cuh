@@ -142,7 +142,7 @@ size_t flat_tensor_bytes(int H, int C, int n_img);
 FlatTensor make_flat_tensor(uint8_t* base, int H, int C, int n_img);
 // conv_pair.cu
 int launch_conv_pair(const ConvParams& p, int cout, int mode, cudaStream_t st);
-int pair_kernel_enabled();
+int pair_kernel_enabled(int cout, int mode);
 void pack_pair_blob(const std::vector<uint16_t>& blob, int cout, const std::vector<int>& stage_ntaps, int G, int kind,
                     uint16_t (*to_half)(float), float (*from_bf)(uint16_t), std::vector<uint16_t>& out);
 // tail.cu
