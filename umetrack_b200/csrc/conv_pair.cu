@@ -552,7 +552,7 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
   const size_t a = (((size_t)p.patch_rows * 16 * (split ? 4 : 2)) + 127) & ~(size_t)127;
   const size_t fixed = 1024 + ((size_t)cout * 4 + 127) / 128 * 128;
   const size_t b = (size_t)p.G * tap_bytes;
-  int n_a = (cout <= 64) ? 6 : 4;
+  int n_a = split ? 3 : 4;   // split mode: deep weight pipelines matter more than deep A pipelines (tools/ab_conv.py: +4..12 % over 4-6 A stages)
   if (const char* e = getenv("UMT_PAIR_NA")) n_a = std::max(2, atoi(e));
   while (n_a > 2 && fixed + a * n_a + b * 2 > budget) --n_a;
   long long nb = ((long long)budget - (long long)fixed - (long long)(a * n_a)) / (long long)b;
