@@ -191,3 +191,31 @@ def test_uint8_crops_give_the_same_result_as_their_float_conversion():
         fd, desc = _inputs(b)
         outs.append(model.regress_pose_use_skeleton(fd, desc, skel))
     assert torch.equal(outs[0].joint_angles, outs[1].joint_angles) and torch.equal(outs[0].wrist_xfs, outs[1].wrist_xfs)
+
+
+def test_fp16_mode_refuses_weights_and_reports_activations_outside_the_half_range():
+    """UMT_MODE_FP16 keeps activations and BN-folded weights in IEEE half: a weight beyond 65504 is
+    refused when the mode is used, an activation beyond it is reported through the status word (the
+    fp32-equivalent and bf16 modes are unaffected)."""
+    from umetrack_b200 import native
+    imgs = synthetic.make_model_batch(2, seed=3)["left_images"].cuda()
+    sd = synthetic.make_state_dict(0)
+    big_w = dict(sd)
+    key = "_feature_extractor._image_backbone.0._layers.1.0.conv1.weight"
+    big_w[key] = sd[key] * 1e7
+    m = UmeTrackModel(big_w).to("cuda")
+    m.encode(imgs)                                   # fp32-equivalent mode still runs
+    with pytest.raises(native.NativeError, match="half range"):
+        m.set_mode("fp16").encode(imgs)
+    big_a = dict(sd)
+    key = "_feature_extractor._image_backbone.0._layers.0.1.bias"
+    big_a[key] = sd[key] + 1e5                       # BatchNorm shift: weights stay small, the stem's outputs do not
+    m = UmeTrackModel(big_a).to("cuda").set_mode("fp16")
+    m.encode(imgs)
+    with pytest.raises(native.NativeError, match="half range"):
+        m.check_status()
+    m.set_mode("bf16").encode(imgs)
+    m.check_status()                                 # bf16 has the float32 exponent range
+    ok = UmeTrackModel(sd).to("cuda").set_mode("fp16")
+    ok.encode(imgs)
+    ok.check_status()

@@ -33,6 +33,9 @@ from .model import InputFrameDesc, InputSkeletonData
 from .skinning import fk_landmarks_device
 
 
+_NEUTRAL_CACHE: Dict[tuple, torch.Tensor] = {}
+
+
 def crop_cameras_raw(hand_model: HandModel, ja: torch.Tensor, wr: torch.Tensor, is_right: torch.Tensor,
                      valid: torch.Tensor, frame_idx: torch.Tensor, intr: torch.Tensor, c2w: torch.Tensor,
                      angles: torch.Tensor, width: int, height: int,
@@ -46,7 +49,13 @@ def crop_cameras_raw(hand_model: HandModel, ja: torch.Tensor, wr: torch.Tensor, 
     n = ja.shape[0]
     n_cam = intr.shape[0]
     # three poses per item: given, neutral, open (perspective_crop.py:89-115)
-    neutral = neutral_joint_angles(hand_model).to(device=device, dtype=torch.float32)
+    lim = hand_model.joint_limits
+    key = (lim.data_ptr(), lim._version, str(device))
+    neutral = _NEUTRAL_CACHE.get(key)
+    if neutral is None:                       # one upload per hand model, not per frame
+        if len(_NEUTRAL_CACHE) > 64:
+            _NEUTRAL_CACHE.clear()
+        neutral = _NEUTRAL_CACHE[key] = neutral_joint_angles(hand_model).to(device=device, dtype=torch.float32)
     poses = torch.stack([ja, neutral.expand(n, 22), torch.zeros((n, 22), device=device)], dim=1)
     wrists = wr.reshape(n, 1, 4, 4).expand(n, 3, 4, 4)
     n_pose = opts.num_crop_points // 21

@@ -288,6 +288,7 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
     // ===== epilogue (both CTAs): own 128 rows of the accumulator -> bias / residual / ReLU -> global =====
     const int lgrp = warp & 3;
     int tc = 0;
+    bool fp16_over = false;
     constexpr int kStep = MERGE ? 16 : 32, kRows = kStep / 8;
     for (int tile = pair_id; tile < P.n_tiles; tile += n_pairs, ++tc) {
       const int buf = tc % n_buf;
@@ -356,6 +357,12 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
             }
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], lo_clamp);
+            if (MODE == UMT_MODE_FP16) {   // a value beyond the half range would be stored as inf
+              float mx = 0.f;
+#pragma unroll
+              for (int e = 0; e < 8; ++e) mx = fmaxf(mx, fabsf(f[e]));
+              fp16_over |= (mx > 65504.f);
+            }
             store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
           }
         }
@@ -365,6 +372,8 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
       __syncwarp();
       if (lane == 0) mbar_arrive_leader(acc_empty(buf));   // 8 arrivals (4 warps x 2 CTAs) free the buffer
     }
+    if (MODE == UMT_MODE_FP16 && P.status && __any_sync(0xFFFFFFFFu, fp16_over) && lane == 0)
+      atomicOr(P.status, (unsigned)UMT_STATUS_FP16_RANGE);
   }
   tc_fence_before();
   __syncthreads();
@@ -450,7 +459,16 @@ template <int COUT, int MODE, int S>
 static int launch_pair_s(const PairParams& p, cudaStream_t st) {
   const size_t smem = pair_smem_bytes(p, COUT, MODE == UMT_MODE_FP32_EQUIV);
   void (*kernel)(PairParams) = p.res_epi ? conv_pair_kernel<COUT, MODE, kEpiResidual, S> : conv_pair_kernel<COUT, MODE, kEpiPlain, S>;
-  UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  {  // opt-in shared-memory size: once per device and kernel (and when it grows)
+    static size_t have[2][64] = {};
+    int dev = 0;
+    UMT_CUDA_TRY(cudaGetDevice(&dev));
+    const int epi = p.res_epi ? 1 : 0;
+    if (dev < 0 || dev >= 64 || have[epi][dev] < smem) {
+      UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (dev >= 0 && dev < 64) have[epi][dev] = smem;
+    }
+  }
   const int pairs = std::max(1, std::min(p.n_tiles, pair_sm_count()));   // two CTAs per SM = one pair per SM on average
   kernel<<<2 * pairs, kPairThreads, smem, st>>>(p);
   return check_launch("conv_pair_kernel");
@@ -521,6 +539,7 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
   p.patch_rows = p.n_box * p.box_rows;
   p.relu = c.relu; p.res_epi = c.res_epi; p.phase_out = c.phase_out;
   p.bias = c.bias;
+  p.status = c.status;
   p.res = c.res;
   for (int i = 0; i < 4; ++i) p.out[i] = c.out[i];
   if (c.n_stages > kPairMaxStages) return fail(UMT_ERR_INVALID, "pair conv: %d stages", c.n_stages);

@@ -83,6 +83,7 @@ extern "C" int umt_model_encode_static(umt_model* m, int mode, const float* imag
   // The weights live on one device; the scratch address below is resolved for the CURRENT device.
   // A mismatch would hand kernels pointers of two different devices.
   UMT_TRY(umt::check_device(m, "umt_model_encode_static"));
+  UMT_TRY(umt::check_mode(m, mode));
   uint8_t* scratch = nullptr;
   UMT_TRY(static_scratch_for_current_device(&scratch));
   cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -313,6 +313,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     // ===== epilogue: TMEM -> registers -> bias / ReLU -> split bf16 -> global =====
     const int lgrp = warp & 3;  // TMEM lane group this warp may read
     int tc = 0;
+    bool fp16_over = false;
     long long w_full = 0, t_begin = clock64();
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
       const int buf = tc % n_buf;
@@ -393,6 +394,12 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
               }
 #pragma unroll
               for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], lo_clamp);
+              if (MODE == UMT_MODE_FP16 && EPI != kEpiDense) {   // a value beyond the half range would be stored as inf
+                float mx = 0.f;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) mx = fmaxf(mx, fabsf(f[e]));
+                fp16_over |= (mx > 65504.f);
+              }
               if (EPI == kEpiDense) {
                 // float32 NCHW output [n, dense_c, H, W]: lanes hold consecutive pixels, so for each
                 // channel the warp writes (nearly) consecutive floats
@@ -413,6 +420,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty(buf));   // 4 arrivals (one per epilogue warp) free the buffer
     }
+    if (MODE == UMT_MODE_FP16 && P.status && __any_sync(0xFFFFFFFFu, fp16_over) && lane == 0)
+      atomicOr(P.status, (unsigned)UMT_STATUS_FP16_RANGE);
     if (P.dbg && warp == 4 && lane == 0) { P.dbg[blockIdx.x * 16 + 8] = w_full; P.dbg[blockIdx.x * 16 + 9] = clock64() - t_begin; }
   }
   tc_fence_before();
@@ -433,6 +442,7 @@ static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
   return 1024 + bias + a * p.n_a + b * p.n_b;
 }
 
+constexpr int kMaxDevices = 64;
 static long long* g_conv_dbg = nullptr;   // set by umt_debug_set_conv_timeline (tools only)
 void set_conv_debug_buffer(long long* p) { g_conv_dbg = p; }
 
@@ -459,7 +469,16 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   }
   ConvParams pd = p;
   pd.dbg = g_conv_dbg;
-  UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  {  // the opt-in shared-memory size is a per-device attribute of each kernel: set it once (and when it grows)
+    static size_t have[3][kMaxDevices] = {};
+    const int epi = p.dense_out ? kEpiDense : p.res_epi ? kEpiResidual : kEpiPlain;
+    int dev = 0;
+    UMT_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices || have[epi][dev] < smem) {
+      UMT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (dev >= 0 && dev < kMaxDevices) have[epi][dev] = smem;
+    }
+  }
   int grid = std::min(p.n_tiles, sm_count() * std::max(1, p.occ));
   grid = std::max(p.cluster, grid / p.cluster * p.cluster);
   cudaLaunchConfig_t cfg{};
@@ -637,7 +656,7 @@ constexpr int kStemSmem = kStemStageOff + kStemDepth * 8192;   // dynamic shared
 template <int MODE>
 __global__ void __launch_bounds__(kStemThreads, 2)
 stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __restrict__ wpack,
-                 const float* __restrict__ bias, FlatTensor out) {
+                 const float* __restrict__ bias, FlatTensor out, unsigned* __restrict__ status) {
   constexpr bool SPLIT = (MODE == UMT_MODE_FP32_EQUIV);
   extern __shared__ __align__(128) uint8_t smem[];
   float* s_bias = reinterpret_cast<float*>(smem + 256);
@@ -771,6 +790,7 @@ stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __r
     // ===== epilogue: max over the four pool members, + bias, ReLU, planar rows =====
     const int lgrp = warp & 3;
     int it = 0;
+    bool fp16_over = false;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int buf = it & 1;
       const long long p = (long long)tile * 128 + lgrp * 32 + lane;
@@ -798,6 +818,7 @@ stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __r
               const float m = fmaxf(fmaxf(__uint_as_float(v0[i]), __uint_as_float(v1[i])),
                                     fmaxf(__uint_as_float(v2[i]), __uint_as_float(v3[i])));
               f[e] = fmaxf(m + s_bias[c0 + i], 0.f);
+              if (MODE == UMT_MODE_FP16) fp16_over |= (f[e] > 65504.f);
             }
             store_row8<MODE>(out, (c0 >> 3) + h, row, f);
           }
@@ -807,6 +828,8 @@ stem_umma_kernel(const float* __restrict__ images, int n_img, const uint8_t* __r
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty(buf));
     }
+    if (MODE == UMT_MODE_FP16 && status && __any_sync(0xFFFFFFFFu, fp16_over) && lane == 0)
+      atomicOr(status, (unsigned)UMT_STATUS_FP16_RANGE);
   }
   tc_fence_before();
   __syncthreads();
@@ -1116,6 +1139,7 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
             const float v = bf2f(blob[src + slab_index(L.cout, pl, 0, co, e)]) +
                             bf2f(blob[src + slab_index(L.cout, pl, 1, co, e)]);   // hi + lo == the folded fp32 weight (to 2^-17)
             const uint16_t hv = f2h(v);
+            if (std::fabs(v) > 65504.f) m->fp16_weights_ok = false;
             h1[(size_t)k * half + ((size_t)pl * L.cout + co) * 8 + e] = hv;
           }
     UMT_CUDA_TRY(cudaMalloc(&L.d_weights_h16, h1.size() * 2));
@@ -1204,6 +1228,7 @@ int encoder_build(umt_model* m, const float* const* t) {
           bf[o] = hi;
           bf[(size_t)2 * 128 * 8 + o] = f2bf(w - bf2f(hi));
           h16[o] = f2h(w);
+          if (std::fabs(w) > 65504.f) m->fp16_weights_ok = false;
         }
     UMT_CUDA_TRY(cudaMalloc(&m->tw.stem_pack_bf, bf.size() * 2));
     m->owned.push_back(m->tw.stem_pack_bf);
@@ -1327,6 +1352,7 @@ static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, int 
   }
   if (L.res_buf >= 0) { p.src[2] = m->buf[g][L.res_buf]; p.res = p.src[2]; }
   p.bias = L.d_bias;
+  p.status = m->d_status;
   p.n_pos = n_img * (p.H + 1) * (p.W + 1);
   finalize_conv_params(p, L, mode);
 }
@@ -1392,19 +1418,26 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
   if (!env_int("UMT_STEM_SIMT", 0)) {
     const int tiles = (int)((px + 127) / 128);
     const int grid = std::max(1, std::min(tiles, 2 * sm_count()));
-    // (per launch, like launch_conv_t: the attribute belongs to the current device)
+    {  // once per device and mode (the attribute belongs to the device)
+      static bool done[3][kMaxDevices] = {};
+      int dev = 0;
+      UMT_CUDA_TRY(cudaGetDevice(&dev));
+      if (dev < 0 || dev >= kMaxDevices || !done[mode][dev]) {
+        if (mode == UMT_MODE_FP32_EQUIV)
+          UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP32_EQUIV>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+        else if (mode == UMT_MODE_BF16)
+          UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+        else
+          UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+        if (dev >= 0 && dev < kMaxDevices) done[mode][dev] = true;
+      }
+    }
     if (mode == UMT_MODE_FP32_EQUIV)
-      UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP32_EQUIV>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+      stem_umma_kernel<UMT_MODE_FP32_EQUIV><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0], m->d_status);
     else if (mode == UMT_MODE_BF16)
-      UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
+      stem_umma_kernel<UMT_MODE_BF16><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0], m->d_status);
     else
-      UMT_CUDA_TRY(cudaFuncSetAttribute(stem_umma_kernel<UMT_MODE_FP16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmem));
-    if (mode == UMT_MODE_FP32_EQUIV)
-      stem_umma_kernel<UMT_MODE_FP32_EQUIV><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
-    else if (mode == UMT_MODE_BF16)
-      stem_umma_kernel<UMT_MODE_BF16><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_bf, m->tw.stem_b, m->buf[0][0]);
-    else
-      stem_umma_kernel<UMT_MODE_FP16><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_h16, m->tw.stem_b, m->buf[0][0]);
+      stem_umma_kernel<UMT_MODE_FP16><<<grid, kStemThreads, kStemSmem, st>>>(images, n_img, m->tw.stem_pack_h16, m->tw.stem_b, m->buf[0][0], m->d_status);
   } else if (mode == UMT_MODE_FP32_EQUIV)
     stem_kernel<UMT_MODE_FP32_EQUIV><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
   else if (mode == UMT_MODE_BF16)

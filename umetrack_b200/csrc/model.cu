@@ -92,6 +92,14 @@ int tensor_index(const char* name) {
   return it == idx.end() ? -1 : it->second;
 }
 
+// UMT_MODE_FP16 needs every BatchNorm-folded weight inside the half range
+int check_mode(const umt_model* m, int mode) {
+  if (mode == UMT_MODE_FP16 && !m->fp16_weights_ok)
+    return fail(UMT_ERR_UNSUPPORTED, "UMT_MODE_FP16: a BatchNorm-folded weight exceeds the half range (65504); "
+                                     "use UMT_MODE_FP32_EQUIV or UMT_MODE_BF16 for these weights");
+  return UMT_OK;
+}
+
 float* upload(umt_model* m, const std::vector<float>& v) {
   float* d = nullptr;
   if (cudaMalloc(&d, v.size() * sizeof(float)) != cudaSuccess) {
@@ -262,6 +270,7 @@ extern "C" int umt_model_encode(umt_model* m, int mode, const float* images, int
   if (mode < UMT_MODE_FP32_EQUIV || mode > UMT_MODE_FP16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_encode: no workspace bound");
   UMT_TRY(check_device(m, "umt_model_encode"));
+  UMT_TRY(check_mode(m, mode));
   if (n_img < 0) return fail(UMT_ERR_INVALID, "umt_model_encode: n_img=%d", n_img);
   m->launches = 0;
   if (n_img == 0) return UMT_OK;
@@ -274,6 +283,7 @@ extern "C" int umt_model_encode_u8(umt_model* m, int mode, const uint8_t* images
   if (mode < UMT_MODE_FP32_EQUIV || mode > UMT_MODE_FP16) return fail(UMT_ERR_INVALID, "bad mode %d", mode);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_encode_u8: no workspace bound");
   UMT_TRY(check_device(m, "umt_model_encode_u8"));
+  UMT_TRY(check_mode(m, mode));
   if (((uintptr_t)images_u8 & 15) != 0) return fail(UMT_ERR_INVALID, "umt_model_encode_u8: images must be 16-byte aligned");
   if (n_img < 0) return fail(UMT_ERR_INVALID, "umt_model_encode_u8: n_img=%d", n_img);
   m->launches = 0;
@@ -295,6 +305,7 @@ static int model_forward(umt_model* m, int mode, int head, const float* images, 
     return fail(UMT_ERR_INVALID, "bad head %d", head);
   if (!m->ws) return fail(UMT_ERR_INVALID, "umt_model_forward: no workspace bound");
   UMT_TRY(check_device(m, "umt_model_forward"));
+  UMT_TRY(check_mode(m, mode));
   if (n_img <= 0 || n_samples <= 0 || n_img > m->ws_max_images || n_samples > m->ws_max_samples)
     return fail(UMT_ERR_INVALID, "umt_model_forward: n_img=%d n_samples=%d exceed the bound workspace (%d, %d)",
                 n_img, n_samples, m->ws_max_images, m->ws_max_samples);

@@ -41,6 +41,7 @@ struct ConvParams {
   int dense_c;
   long long* dbg;           // optional [grid][16] cycle counters (tools/conv_timeline.py); nullptr in production
   const float* bias;        // [COUT]
+  unsigned* status;         // device status word (UMT_STATUS_*), may be null
   int H, W;                 // output-domain geometry
   int n_pos;                // valid positions: n_img * (H+1) * (W+1)
   int S;                    // 128-row sub-tiles per CTA
@@ -119,6 +120,7 @@ struct umt_model {
   std::vector<umt::ConvLayer> tail_convs; // fusion(3), temporal(3), regressor_k(4), regressor_u(4)
   umt::FlatTensor tail_flat[3]{};         // 6x6 planar flat scratch, 144 channels capacity
   int launches = 0;
+  bool fp16_weights_ok = true;            // no BN-folded weight saturates in half precision (UMT_MODE_FP16 allowed)
   int device = -1;                        // device the weights were uploaded to (umt_model_create)
   unsigned* d_status = nullptr;           // sticky UMT_STATUS_* bits set by kernels, read by umt_model_status
   umt_model* static_view = nullptr;       // host-side view used by umt_model_encode_static (no device memory)
@@ -154,7 +156,8 @@ int tail_forward(umt_model* m, int head, const float* feats, const float* intrin
                  float* prev_extr, int n_slots, float* out_joint_angles, float* out_wrist,
                  float* out_scale, float* out_sigma, cudaStream_t st);
 // model.cu
-int check_device(const umt_model* m, const char* what);   // current device must be the model's
+int check_device(const umt_model* m, const char* what);
+int check_mode(const umt_model* m, int mode);      // UMT_MODE_FP16 only with weights inside the half range   // current device must be the model's
 int tensor_index(const char* name);   // index into the umt_model_create tensor list, -1 if absent
 float* upload(umt_model* m, const std::vector<float>& v);
 }  // namespace umt

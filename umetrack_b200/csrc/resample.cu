@@ -253,9 +253,15 @@ extern "C" int umt_resample_crops(const uint8_t* src_base, const int64_t* src_of
   if (n_crops == 0) return UMT_OK;
   if (!src_base || !src_offset || !params)
     return umt::fail(UMT_ERR_INVALID, "umt_resample_crops: null input pointer");
-  // per call: the attribute belongs to the current device
-  UMT_CUDA_TRY(cudaFuncSetAttribute(resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    kStageBytes));
+  {  // once per device: the attribute belongs to the device
+    static bool done[64] = {};
+    int dev = 0;
+    UMT_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !done[dev]) {
+      UMT_CUDA_TRY(cudaFuncSetAttribute(resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes));
+      if (dev >= 0 && dev < 64) done[dev] = true;
+    }
+  }
   resample_kernel<<<n_crops * 9, kThreads, kStageBytes, (cudaStream_t)stream>>>(
       src_base, src_offset, src_pitch, src_w, src_h, params, out_u8, out_f32, out_idx);
   return umt::check_launch("resample_kernel");

@@ -167,8 +167,14 @@ class HandTracker:
         self._min_required_vis_landmarks = opts.min_required_vis_landmarks
         self._valid_tracking_history = np.zeros(2, dtype=bool)
         self._device_crop_cameras = True      # False: always build crop cameras with numpy on the host
+        self.use_cuda_graphs = True           # replay the per-frame forward pass as one CUDA graph (same results)
         self._skel_cache = None
         self._last_hands = None
+
+    def _graph_scope(self):
+        import contextlib
+        scope = getattr(self._model, "frame_graph_scope", None)
+        return scope() if (scope is not None and self.use_cuda_graphs) else contextlib.nullcontext()
 
     def reset_history(self) -> None:
         self._valid_tracking_history[:] = False
@@ -239,16 +245,18 @@ class HandTracker:
             self.reset_history()
             return TrackingResult()
         data, desc, skel = self._make_inputs(sample, hand_model, crop_cameras)
-        out = self._model.regress_pose_use_skeleton(data, desc, skel)
-        return self._gen_tracking_result(out, self._last_hands, crop_cameras)
+        with self._graph_scope():      # one CUDA-graph replay per frame; outputs are read before returning
+            out = self._model.regress_pose_use_skeleton(data, desc, skel)
+            return self._gen_tracking_result(out, self._last_hands, crop_cameras)
 
     def track_frame_and_calibrate_scale(self, sample: InputFrame, crop_cameras) -> TrackingResult:
         if not crop_cameras:
             self.reset_history()
             return TrackingResult()
         data, desc, _ = self._make_inputs(sample, None, crop_cameras)
-        out = self._model.regress_pose_pred_skel_scale(data, desc)
-        return self._gen_tracking_result(out, self._last_hands, crop_cameras)
+        with self._graph_scope():
+            out = self._model.regress_pose_pred_skel_scale(data, desc)
+            return self._gen_tracking_result(out, self._last_hands, crop_cameras)
 
     def _make_inputs(self, sample: InputFrame, hand_model_mm: Optional[HandModel], crop_cameras):
         pairs, intr, extr, ranges, hands = [], [], [], [], []
@@ -265,15 +273,21 @@ class HandTracker:
                 ranges.append([start, len(pairs)])
         hands_np = np.array(hands)
         dev = self._device
+        n, bs = len(pairs), len(hands)
+        # three uploads per frame instead of seven: camera matrices, integer descriptors, memory flags
+        cam = np.concatenate([np.stack(intr).reshape(-1), np.stack(extr).reshape(-1)]).astype(np.float32)
+        cam_d = torch.from_numpy(cam).to(dev)
+        ints = np.concatenate([np.asarray(ranges, dtype=np.int64).reshape(-1), hands_np.astype(np.int64)])
+        ints_d = torch.from_numpy(ints).to(dev)
         data = InputFrameData(
             left_images=warp_views_device(sample.views, pairs, dev),
-            intrinsics=torch.from_numpy(np.stack(intr)).float().to(dev),
-            extrinsics_xf=torch.from_numpy(np.stack(extr)).float().to(dev))
+            intrinsics=cam_d[:9 * n].view(n, 3, 3),
+            extrinsics_xf=cam_d[9 * n:].view(n, 4, 4))
         desc = InputFrameDesc(
-            sample_range=torch.tensor(ranges, dtype=torch.int64, device=dev),
-            memory_idx=torch.from_numpy(hands_np).long().to(dev),
-            use_memory=torch.from_numpy(self._valid_tracking_history[hands_np]).bool().to(dev),
-            hand_idx=torch.from_numpy(hands_np).long().to(dev),
+            sample_range=ints_d[:2 * bs].view(bs, 2),
+            memory_idx=ints_d[2 * bs:],
+            use_memory=torch.from_numpy(self._valid_tracking_history[hands_np]).to(dev),
+            hand_idx=ints_d[2 * bs:],
             n_memory_slots=NUM_HANDS)        # memory_idx is a hand index: the bank always has both slots
         skel = None
         if hand_model_mm is not None:

@@ -110,6 +110,8 @@ class UmeTrackModel:
         self._mem_features = torch.empty(0)
         self._prev_extrinsics = torch.empty(0)
         self.last_launch_count = 0
+        self._frame_graphs = False
+        self._graphs: Dict[tuple, dict] = {}
 
     # ---- nn.Module-like surface the callers use ----------------------------------------------
     def eval(self):
@@ -162,9 +164,35 @@ class UmeTrackModel:
     def cuda(self, index: Optional[int] = None):
         return self.to(torch.device("cuda", torch.cuda.current_device() if index is None else index))
 
+    def enable_frame_graphs(self, on: bool = True):
+        """Latency mode for per-frame callers (HandTracker): a forward pass on at most 8 crops is
+        captured once per shape into a CUDA graph and replayed -- one launch instead of ~45 and no
+        per-call host work in the C library.  The returned tensors are the graph's static outputs:
+        they are overwritten by the next call of the same shape, so read them before calling again
+        (HandTracker copies them to the host straight away)."""
+        self._frame_graphs = bool(on)
+        if not on:
+            self._graphs.clear()
+        return self
+
+    def frame_graph_scope(self):
+        """Context manager: frame graphs on for the calls inside (used by HandTracker, which reads the
+        static outputs before it returns), previous setting restored afterwards."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def scope():
+            prev, self._frame_graphs = self._frame_graphs, True
+            try:
+                yield self
+            finally:
+                self._frame_graphs = prev
+        return scope()
+
     def reset_memory(self):
         self._mem_features = torch.empty(0)
         self._prev_extrinsics = torch.empty(0)
+        self._graphs.clear()
 
     def _release(self):
         if self._handle is not None:
@@ -253,6 +281,8 @@ class UmeTrackModel:
             raise ValueError("memory_idx must be non-negative")
         self._grow_memory(need)
         dev = self._device
+        if (self._frame_graphs and features is None and n_img <= 8 and (skel is not None or head == native.HEAD_UNKNOWN)):
+            return self._forward_graph(head, images, intr, extr, srange, mem_idx, use_mem, hand_idx, skel)
         ja = torch.empty((bs, 22), dtype=torch.float32, device=dev)
         wr = torch.empty((bs, 4, 4), dtype=torch.float32, device=dev)
         sg = torch.empty((bs, 21), dtype=torch.float32, device=dev)
@@ -284,6 +314,61 @@ class UmeTrackModel:
                     native.current_stream_ptr()), "umt_model_forward")
         self.last_launch_count = lib.umt_model_last_launch_count(self._handle)
         return RegressorOutput(joint_angles=ja, wrist_xfs=wr, skel_scales=sc, landmark_uncertainty_sigmas=sg)
+
+    def _forward_graph(self, head, images, intr, extr, srange, mem_idx, use_mem, hand_idx, skel) -> RegressorOutput:
+        """Replay (or capture) the CUDA graph of umt_model_forward for this shape."""
+        dev = self._device
+        n_img, bs = images.shape[0], srange.shape[0]
+        axes = rest = None
+        if head == native.HEAD_KNOWN:
+            axes = self._prep(skel.joint_rotation_axes, torch.float32).reshape(-1, 22, 3)
+            rest = self._prep(skel.joint_rest_positions, torch.float32).reshape(-1, 22, 3)
+        n_skel = 0 if axes is None else axes.shape[0]
+        key = (head, self._mode, n_img, bs, n_skel, images.dtype, self._ws.data_ptr(), self._mem_features.data_ptr(),
+               len(self._mem_features))
+        g = self._graphs.get(key)
+        ins = [images, intr, extr, srange, mem_idx, use_mem, hand_idx] + ([axes, rest] if axes is not None else [])
+        if g is None:
+            if len(self._graphs) > 16:
+                self._graphs.clear()
+            st = [t.clone() for t in ins]
+            out = {"ja": torch.empty((bs, 22), dtype=torch.float32, device=dev),
+                   "wr": torch.empty((bs, 4, 4), dtype=torch.float32, device=dev),
+                   "sg": torch.empty((bs, 21), dtype=torch.float32, device=dev),
+                   "sc": torch.empty((bs,), dtype=torch.float32, device=dev) if head == native.HEAD_UNKNOWN else None}
+            lib = native.lib()
+            fwd = lib.umt_model_forward_u8 if images.dtype == torch.uint8 else lib.umt_model_forward
+
+            def call():
+                native.check(fwd(
+                    self._handle, self._mode, head, native.ptr(st[0]), native.ptr(st[1]), native.ptr(st[2]),
+                    native.ptr(st[3]), native.ptr(st[4]), native.ptr(st[5]), native.ptr(st[6]), n_img, bs,
+                    native.ptr(st[7]) if n_skel else 0, native.ptr(st[8]) if n_skel else 0, n_skel,
+                    native.ptr(self._mem_features), native.ptr(self._prev_extrinsics), len(self._mem_features),
+                    native.ptr(out["ja"]), native.ptr(out["wr"]), native.ptr(out["sc"]), native.ptr(out["sg"]),
+                    native.current_stream_ptr()), "umt_model_forward")
+
+            # one plain call first (per-device kernel attributes, driver entry points), on a copy of the
+            # recurrent state so that the capture below is this call's one and only state update
+            mem, ext = self._mem_features.clone(), self._prev_extrinsics.clone()
+            with torch.cuda.device(dev):
+                call()
+                self._mem_features.copy_(mem)
+                self._prev_extrinsics.copy_(ext)
+                torch.cuda.synchronize(dev)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    call()
+            g = {"graph": graph, "st": st, "out": out, "launches": native.lib().umt_model_last_launch_count(self._handle)}
+            self._graphs[key] = g
+        else:
+            for dst, src in zip(g["st"], ins):
+                dst.copy_(src)
+        g["graph"].replay()
+        self.last_launch_count = g["launches"]
+        o = g["out"]
+        return RegressorOutput(joint_angles=o["ja"], wrist_xfs=o["wr"], skel_scales=o["sc"],
+                               landmark_uncertainty_sigmas=o["sg"])
 
     # ---- the two entry points of the reference ------------------------------------------------
     def regress_pose_use_skeleton(self, frame_data: InputFrameData, frame_desc: InputFrameDesc,
