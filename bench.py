@@ -55,6 +55,9 @@ def ncu_conv_traffic(mode):
     Bytes per launch, like `achieved`."""
     import csv
     import glob
+    note = None
+    if mode == "bf16" and not glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_conv_full_summary_bf16.csv")):
+        mode, note = "fp16", "capture of the fp16 mode: same kernels, same 2-byte operands and activations as bf16"
     mode_id = {"fp32": 0, "bf16": 1, "fp16": 2}[mode]
     for path in sorted(glob.glob(os.path.join(ROOT, "profiles", f"r*_ncu_conv_full_summary_{mode}.csv")), reverse=True):
         tot, n, crops = 0.0, 0, 4096
@@ -69,15 +72,18 @@ def ncu_conv_traffic(mode):
                         rd = (i, scale[h.split("[")[1].rstrip("]")])
                     if h.startswith("dram__bytes_write.sum"):
                         wr = (i, scale[h.split("[")[1].rstrip("]")])
-            if len(r) <= 6 or "conv_umma_kernel<" not in r[0] or rd is None or wr is None:
+            if len(r) <= 6 or not ("conv_umma_kernel<" in r[0] or "conv_pair_kernel<" in r[0]) or rd is None or wr is None:
                 continue
             targs = [int(v) for v in r[0].split("<")[1].split(">")[0].replace("true", "1").replace("false", "0").split(",")]
             if targs[0] in (32, 64, 128, 256) and targs[1] == mode_id and targs[2] != 2:     # backbone launches of this mode
                 tot += float(r[rd[0]]) * rd[1] + float(r[wr[0]]) * wr[1]
                 n += 1
         if n:
-            return {"bytes_per_launch": tot / n, "launches": n, "crops_per_launch": crops,
-                    "source": os.path.relpath(path, ROOT)}
+            out = {"bytes_per_launch": tot / n, "launches": n, "crops_per_launch": crops,
+                   "source": os.path.relpath(path, ROOT)}
+            if note:
+                out["note"] = note
+            return out
     return None
 
 
@@ -579,7 +585,7 @@ def main():
             "peak_sustained": sustained, "frac_vs_sustained": achieved / sustained,
             "traffic": (traffic or {}).get("bytes_per_launch"),
             "traffic_source": traffic,
-            "kernel": "conv_umma_kernel (24 launches per encoder pass)",
+            "kernel": "conv_pair_kernel / conv_umma_kernel (the 24 tcgen05 convolutions of one encoder pass)",
             "peak_source": src + ": `peak` is the bf16 burst figure because the launches are timed one by one with "
                                  "CUDA events at burst clocks (see `clocks`); the sustained figure is given beside it",
             "note": "achieved = algorithmic conv FLOPs (962.6 MFLOP per crop x crops per launch) / sum of the 24 launch "
