@@ -219,3 +219,45 @@ def test_fp16_mode_refuses_weights_and_reports_activations_outside_the_half_rang
     ok = UmeTrackModel(sd).to("cuda").set_mode("fp16")
     ok.encode(imgs)
     ok.check_status()
+
+
+def test_fused_small_batch_tail_and_tensor_core_tail_agree(monkeypatch):
+    """Batches up to 256 samples run the tail as one CTA per sample (csrc/tail_fused.cu, float32 FMAs);
+    larger ones through the tensor-core convolutions of csrc/tail.cu.  Same inputs, same recurrent state:
+    both within the keypoint gate of the oracle and within 1e-3 mm of each other, over three steps with
+    mixed 1/2-view samples and memory resets."""
+    sd = synthetic.make_state_dict(0)
+    hm = hmod.load_hand_model_from_dict(hm_dict())
+    ax, rest = hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None]
+    results = {}
+    for name, limit in (("fused", "256"), ("tensor", "0")):
+        monkeypatch.setenv("UMT_TAIL_FUSED_MAX", limit)
+        model = UmeTrackModel(sd).to("cuda")
+        orc = O.OracleModel(sd)
+        kps, launches = [], []
+        for step in range(3):
+            b = synthetic.make_model_batch(24, seed=600 + step, single_view_every=4)
+            b["use_memory"][:] = step > 0
+            if step == 2:
+                b["use_memory"][::3] = False
+            out = model.regress_pose_use_skeleton(*_inputs(b), InputSkeletonData(ax, rest))
+            launches.append(model.last_launch_count)
+            ref = orc.regress_pose_use_skeleton(b["left_images"], b["intrinsics"], b["extrinsics_xf"], b["sample_range"],
+                                                b["memory_idx"], b["use_memory"], b["hand_idx"], ax, rest)
+            kp = _keypoints_mm(hm, out.joint_angles.cpu(), out.wrist_xfs.cpu())
+            kp_ref = _keypoints_mm(hm, ref["joint_angles"], ref["wrist_xfs"])
+            assert float((kp - kp_ref).abs().max()) < KEYPOINT_TOL_MM, f"{name} step {step}"
+            kps.append(kp)
+        assert float((model._mem_features.cpu() - orc.state.mem).abs().max()) < 5e-4
+        results[name] = (torch.stack(kps), launches)
+        # unknown-skeleton head on the same path
+        g = golden("model_golden.npz")
+        model2 = UmeTrackModel(sd).to("cuda")
+        for step, use_mem in enumerate((False, True)):
+            b = synthetic.make_model_batch(4, seed=200 + step)
+            b["use_memory"][:] = use_mem
+            out = model2.regress_pose_pred_skel_scale(*_inputs(b))
+            assert np.abs(out.skel_scales.cpu().numpy() - g[f"u_scales_{step}"]).max() < 2e-5
+            assert np.abs(out.wrist_xfs.cpu().numpy() - g[f"u_wrist_xfs_{step}"]).max() < 2e-5
+    assert float((results["fused"][0] - results["tensor"][0]).abs().max()) < 1e-3
+    assert results["fused"][1][0] == 26 + 2 and results["tensor"][1][0] == 26 + 15     # launches per forward pass

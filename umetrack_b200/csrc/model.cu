@@ -211,6 +211,15 @@ extern "C" int umt_model_bind_workspace(umt_model* m, void* workspace, size_t by
     return fail(UMT_ERR_INVALID, "umt_model_bind_workspace: %zu bytes given, %zu needed", bytes, need);
   if (((uintptr_t)workspace & 255) != 0)
     return fail(UMT_ERR_INVALID, "umt_model_bind_workspace: workspace must be 256-byte aligned");
+  UMT_TRY(check_device(m, "umt_model_bind_workspace"));
+  {  // the workspace must be memory of the model's own GPU (the kernels' tensor maps are built over it)
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, workspace) != cudaSuccess || attr.type != cudaMemoryTypeDevice ||
+        attr.device != m->device) {
+      cudaGetLastError();
+      return fail(UMT_ERR_INVALID, "umt_model_bind_workspace: workspace is not device memory of GPU %d", m->device);
+    }
+  }
   // halo rows of the activation tensors must read as zero for the whole life of the binding
   UMT_CUDA_TRY(cudaMemsetAsync(workspace, 0, need, (cudaStream_t)stream));
   m->ws = (uint8_t*)workspace;

@@ -97,6 +97,10 @@ struct TailWeights {
   float *skel_w, *skel_b;                 // [144,132] with BN(4) folded, [144]
   float *head_w[2], *head_b[2];           // [n_out, 80] (zero columns for the channel padding), [n_out]
   float *stem_w, *stem_b;                 // [32,9] folded, [32]
+  // float32 weights of the one-CTA-per-sample tail kernel (tail_fused.cu), input-channel major: [ci][tap][co]
+  float *fus_w[3], *fus_b[3];             // fusion 144->108->72->72 (BN folded)
+  float *tmp_w[3], *tmp_b[3];             // temporal 90->90 x3
+  float *reg_w[2][4], *reg_b[2][4];       // regressor_k (C = 76) / regressor_u (C = 72): four 3x3 convs (BN folded)
   uint8_t *stem_pack_bf, *stem_pack_h16;  // tensor-core stem operand [hi|lo][2][128][8] bf16 / [2][128][8] fp16
 };
 
@@ -155,6 +159,13 @@ int tail_forward(umt_model* m, int head, const float* feats, const float* intrin
                  const float* skel_axes, const float* skel_rest, int n_skel, float* mem_state,
                  float* prev_extr, int n_slots, float* out_joint_angles, float* out_wrist,
                  float* out_scale, float* out_sigma, cudaStream_t st);
+// tail_fused.cu
+int tail_fused_max_samples();
+int tail_fused_forward(umt_model* m, int head, const float* feats, const float* intrinsics,
+                       const float* extrinsics, const int64_t* sample_range, const int64_t* memory_idx,
+                       const uint8_t* use_memory, const int64_t* hand_idx, int n_samples, const float* skel,
+                       int n_skel, float* mem_state, float* prev_extr, int n_slots, float* out_joint_angles,
+                       float* out_wrist, float* out_scale, float* out_sigma, cudaStream_t st);
 // model.cu
 int check_device(const umt_model* m, const char* what);
 int check_mode(const umt_model* m, int mode);      // UMT_MODE_FP16 only with weights inside the half range   // current device must be the model's

@@ -19,73 +19,9 @@
 
 #include "model.cuh"
 #include "flat.cuh"
+#include "tail_math.cuh"
 
 namespace umt {
-
-constexpr int kPix = 36;
-constexpr int kPos = 49;   // positions per sample in the 6x6 planar flat raster (7 x 7)
-
-// ------------------------------------------------------------------------------------------
-// small matrix helpers (double precision, per thread)
-// ------------------------------------------------------------------------------------------
-__device__ void mat4_mul(const double* a, const double* b, double* c) {
-  for (int i = 0; i < 4; ++i)
-    for (int j = 0; j < 4; ++j) {
-      double s = 0;
-      for (int k = 0; k < 4; ++k) s += a[i * 4 + k] * b[k * 4 + j];
-      c[i * 4 + j] = s;
-    }
-}
-
-// general 4x4 inverse by Gauss-Jordan with partial pivoting; returns false if singular
-__device__ bool mat4_inv(const double* a, double* inv) {
-  double m[4][8];
-  for (int i = 0; i < 4; ++i)
-    for (int j = 0; j < 4; ++j) {
-      m[i][j] = a[i * 4 + j];
-      m[i][4 + j] = (i == j) ? 1.0 : 0.0;
-    }
-  for (int c = 0; c < 4; ++c) {
-    int piv = c;
-    double best = fabs(m[c][c]);
-    for (int r = c + 1; r < 4; ++r)
-      if (fabs(m[r][c]) > best) {
-        best = fabs(m[r][c]);
-        piv = r;
-      }
-    if (best < 1e-300) return false;
-    if (piv != c)
-      for (int j = 0; j < 8; ++j) {
-        double t = m[c][j];
-        m[c][j] = m[piv][j];
-        m[piv][j] = t;
-      }
-    const double d = 1.0 / m[c][c];
-    for (int j = 0; j < 8; ++j) m[c][j] *= d;
-    for (int r = 0; r < 4; ++r) {
-      if (r == c) continue;
-      const double f = m[r][c];
-      if (f != 0.0)
-        for (int j = 0; j < 8; ++j) m[r][j] -= f * m[c][j];
-    }
-  }
-  for (int i = 0; i < 4; ++i)
-    for (int j = 0; j < 4; ++j) inv[i * 4 + j] = m[i][4 + j];
-  return true;
-}
-
-__device__ void load_mat4(const float* p, double* m) {
-  for (int i = 0; i < 16; ++i) m[i] = (double)p[i];
-}
-
-// FTL on a [3*n] point cloud stored as three consecutive blocks X|Y|Z of n floats
-// (lib/models/model_utils.py:83-95): out = R * p + t, with xf the top 3x4 of a 4x4 in float32.
-__device__ __forceinline__ void ftl_point(const float* xf, float x, float y, float z, float& ox,
-                                          float& oy, float& oz) {
-  ox = xf[0] * x + xf[1] * y + xf[2] * z + xf[3];
-  oy = xf[4] * x + xf[5] * y + xf[6] * z + xf[7];
-  oz = xf[8] * x + xf[9] * y + xf[10] * z + xf[11];
-}
 
 // ------------------------------------------------------------------------------------------
 // sample tile <-> planar flat (6x6 geometry, split bf16)
@@ -283,80 +219,6 @@ temporal_finish_kernel(FlatTensor tout /* 96 ch */, const int64_t* __restrict__ 
 // ------------------------------------------------------------------------------------------
 // 5. head: conv1x1(C -> n_out) + global average pool, decoders, Procrustes, world recovery
 // ------------------------------------------------------------------------------------------
-__device__ void jacobi_svd3(const double* A, double* U, double* S, double* V) {
-  // one-sided Jacobi: rotate columns of W = A*V until orthogonal; then W = U*diag(S)
-  double W[9];
-  for (int i = 0; i < 9; ++i) {
-    W[i] = A[i];
-    V[i] = (i % 4 == 0) ? 1.0 : 0.0;
-  }
-  for (int sweep = 0; sweep < 30; ++sweep) {
-    double off = 0.0;
-    for (int p = 0; p < 2; ++p)
-      for (int q = p + 1; q < 3; ++q) {
-        double a = 0, b = 0, c = 0;
-        for (int i = 0; i < 3; ++i) {
-          a += W[i * 3 + p] * W[i * 3 + p];
-          b += W[i * 3 + q] * W[i * 3 + q];
-          c += W[i * 3 + p] * W[i * 3 + q];
-        }
-        off = fmax(off, fabs(c) / (sqrt(a * b) + 1e-300));
-        if (fabs(c) < 1e-300) continue;
-        const double zeta = (b - a) / (2.0 * c);
-        const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-        const double cs = 1.0 / sqrt(1.0 + t * t), sn = cs * t;
-        for (int i = 0; i < 3; ++i) {
-          const double wp = W[i * 3 + p], wq = W[i * 3 + q];
-          W[i * 3 + p] = cs * wp - sn * wq;
-          W[i * 3 + q] = sn * wp + cs * wq;
-          const double vp = V[i * 3 + p], vq = V[i * 3 + q];
-          V[i * 3 + p] = cs * vp - sn * vq;
-          V[i * 3 + q] = sn * vp + cs * vq;
-        }
-      }
-    if (off < 1e-15) break;
-  }
-  for (int j = 0; j < 3; ++j) {
-    S[j] = sqrt(W[j] * W[j] + W[3 + j] * W[3 + j] + W[6 + j] * W[6 + j]);
-  }
-  // sort singular values descending (torch.svd order) so the reflection fix hits the smallest
-  int order[3] = {0, 1, 2};
-  for (int i = 0; i < 2; ++i)
-    for (int j = i + 1; j < 3; ++j)
-      if (S[order[j]] > S[order[i]]) {
-        int t = order[i];
-        order[i] = order[j];
-        order[j] = t;
-      }
-  double Ws[9], Vs[9], Ss[3];
-  for (int j = 0; j < 3; ++j) {
-    Ss[j] = S[order[j]];
-    for (int i = 0; i < 3; ++i) {
-      Ws[i * 3 + j] = W[i * 3 + order[j]];
-      Vs[i * 3 + j] = V[i * 3 + order[j]];
-    }
-  }
-  for (int j = 0; j < 3; ++j) S[j] = Ss[j];
-  for (int i = 0; i < 9; ++i) V[i] = Vs[i];
-  // U columns; a vanishing third singular value gets u2 = u0 x u1
-  for (int j = 0; j < 3; ++j) {
-    if (Ss[j] > 1e-12 * (Ss[0] + 1e-300)) {
-      for (int i = 0; i < 3; ++i) U[i * 3 + j] = Ws[i * 3 + j] / Ss[j];
-    } else if (j == 2) {
-      U[2] = U[3] * U[7] - U[6] * U[4];
-      U[5] = U[6] * U[1] - U[0] * U[7];
-      U[8] = U[0] * U[4] - U[3] * U[1];
-    } else {
-      for (int i = 0; i < 3; ++i) U[i * 3 + j] = (i == j) ? 1.0 : 0.0;
-    }
-  }
-}
-
-__device__ double det3(const double* m) {
-  return m[0] * (m[4] * m[8] - m[5] * m[7]) - m[1] * (m[3] * m[8] - m[5] * m[6]) +
-         m[2] * (m[3] * m[7] - m[4] * m[6]);
-}
-
 __global__ void __launch_bounds__(128)
 head_kernel(FlatTensor x /* 80 ch */, int C, const float* __restrict__ w /* [n_out][C] */,
             const float* __restrict__ bias, int n_out, int with_scale,
@@ -386,74 +248,8 @@ head_kernel(FlatTensor x /* 80 ch */, int C, const float* __restrict__ w /* [n_o
     sRaw[o] = a;
   }
   __syncthreads();
-  const int t = threadIdx.x;
-  if (t < 22) out_angles[(size_t)b * 22 + t] = (t < 20) ? sRaw[t] : 0.f;  // regressor.py:76-86
-  const int sig0 = with_scale ? 42 : 41;
-  if (t < 21) {  // clamp(softplus(x), 1e-5)  (regressor.py:117-121); torch threshold = 20
-    const float v = sRaw[sig0 + t];
-    const float sp = (v > 20.f) ? v : log1pf(expf(v));
-    out_sigma[(size_t)b * 21 + t] = fmaxf(sp, 1e-5f);
-  }
-  if (t == 32 && with_scale && out_scale) out_scale[b] = expf(sRaw[41]);  // regressor.py:106-114
-  if (t == 64) {
-    // Procrustes (model_utils.py:17-54) of the 7 template points (regressor.py:19-47) onto the
-    // predicted ones, then inv(E0) * X and the right-hand flip (umetrack_model.py:77-90)
-    const double k = 0.1, d = 0.1 / sqrt(2.0);
-    const double P[21] = {0, 0, 0, k, 0, 0, 0, k, 0, 0, 0, k, -d, -d, 0, -d, 0, -d, 0, -d, -d};
-    float Pf[21], Q[21];
-    for (int i = 0; i < 21; ++i) {
-      Pf[i] = (float)P[i];  // the reference keeps the template in float32
-      Q[i] = sRaw[20 + i];
-    }
-    double mp[3] = {0, 0, 0}, mq[3] = {0, 0, 0};
-    for (int i = 0; i < 7; ++i)
-      for (int c = 0; c < 3; ++c) {
-        mp[c] += Pf[i * 3 + c];
-        mq[c] += Q[i * 3 + c];
-      }
-    for (int c = 0; c < 3; ++c) {
-      mp[c] /= 7.0;
-      mq[c] /= 7.0;
-    }
-    double Hm[9] = {0};
-    for (int i = 0; i < 7; ++i)
-      for (int r = 0; r < 3; ++r)
-        for (int c = 0; c < 3; ++c) Hm[r * 3 + c] += (Pf[i * 3 + r] - mp[r]) * (Q[i * 3 + c] - mq[c]);
-    double U[9], S[3], V[9];
-    jacobi_svd3(Hm, U, S, V);
-    double VUt[9];
-    for (int r = 0; r < 3; ++r)
-      for (int c = 0; c < 3; ++c) {
-        double s = 0;
-        for (int j = 0; j < 3; ++j) s += V[r * 3 + j] * U[c * 3 + j];
-        VUt[r * 3 + c] = s;
-      }
-    const double dsign = det3(VUt);
-    double R[9];
-    for (int r = 0; r < 3; ++r)
-      for (int c = 0; c < 3; ++c) {
-        double s = 0;
-        for (int j = 0; j < 3; ++j) s += V[r * 3 + j] * (j == 2 ? dsign : 1.0) * U[c * 3 + j];
-        R[r * 3 + c] = s;
-      }
-    double X[16] = {0};
-    for (int r = 0; r < 3; ++r) {
-      for (int c = 0; c < 3; ++c) X[r * 4 + c] = R[r * 3 + c];
-      X[r * 4 + 3] = mq[r] - (R[r * 3] * mp[0] + R[r * 3 + 1] * mp[1] + R[r * 3 + 2] * mp[2]);
-    }
-    X[15] = 1.0;
-    double E0[16], Einv[16], Wd[16];
-    const int r0 = (int)sample_range[2 * b];
-    load_mat4(extrinsics + (size_t)r0 * 16, E0);
-    const bool ok = mat4_inv(E0, Einv);
-    mat4_mul(Einv, X, Wd);
-    const double flip = (hand_idx[b] == 1) ? -1.0 : 1.0;
-    for (int r = 0; r < 4; ++r)
-      for (int c = 0; c < 4; ++c) {
-        double v = Wd[r * 4 + c] * (c == 0 ? flip : 1.0);
-        out_wrist[(size_t)b * 16 + r * 4 + c] = ok ? (float)v : nanf("");
-      }
-  }
+  head_decode(threadIdx.x, sRaw, b, with_scale, extrinsics, sample_range, hand_idx, out_angles, out_wrist, out_scale,
+              out_sigma);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -496,8 +292,43 @@ static int add_tail_conv(umt_model* m, const Folded& f, bool relu, bool residual
   return UMT_OK;
 }
 
+// [co][ci][k] -> [ci][k][co] on the device (tail_fused.cu reads consecutive output channels per lane)
+static float* upload_ci_major(umt_model* m, const Folded& f) {
+  const int kk = f.ks * f.ks;
+  std::vector<float> w((size_t)f.cin * kk * f.cout);
+  for (int co = 0; co < f.cout; ++co)
+    for (int ci = 0; ci < f.cin; ++ci)
+      for (int k = 0; k < kk; ++k) w[((size_t)ci * kk + k) * f.cout + co] = f.w[((size_t)co * f.cin + ci) * kk + k];
+  return upload(m, w);
+}
+
 int tail_build(umt_model* m, const float* const* t) {
   m->tail_convs.clear();
+  {  // unpadded float32 copies for the fused small-batch kernel
+    const std::string fu = "_feature_extractor._multi_view_fusion.", te = "_temporal._temporal_module.";
+    const Folded f[3] = {folded_padded(t, fu + "0", fu + "1", 108, 144, 1, true, 108, 144),
+                         folded_padded(t, fu + "3", fu + "4", 72, 108, 1, true, 72, 108),
+                         folded_padded(t, fu + "6", "", 72, 72, 1, true, 72, 72)};
+    for (int i = 0; i < 3; ++i) {
+      m->tw.fus_w[i] = upload_ci_major(m, f[i]);
+      m->tw.fus_b[i] = upload(m, f[i].b);
+      const Folded g = folded_padded(t, te + std::to_string(2 * i), "", 90, 90, 1, true, 90, 90);
+      m->tw.tmp_w[i] = upload_ci_major(m, g);
+      m->tw.tmp_b[i] = upload(m, g.b);
+      if (!m->tw.fus_w[i] || !m->tw.fus_b[i] || !m->tw.tmp_w[i] || !m->tw.tmp_b[i]) return UMT_ERR_CUDA;
+    }
+    const char* heads[2] = {"_regressor_k", "_regressor_u"};
+    const int hc[2] = {76, 72};
+    for (int h = 0; h < 2; ++h)
+      for (int c = 0; c < 4; ++c) {
+        const std::string pre = std::string(heads[h]) + "._pose_regression_layers." + std::to_string(c / 2);
+        const std::string cv = (c & 1) ? ".conv2" : ".conv1", bn = (c & 1) ? ".bn2" : ".bn1";
+        const Folded g = folded_padded(t, pre + cv, pre + bn, hc[h], hc[h], 3, false, hc[h], hc[h]);
+        m->tw.reg_w[h][c] = upload_ci_major(m, g);
+        m->tw.reg_b[h][c] = upload(m, g.b);
+        if (!m->tw.reg_w[h][c] || !m->tw.reg_b[h][c]) return UMT_ERR_CUDA;
+      }
+  }
   const std::string fu = "_feature_extractor._multi_view_fusion.";
   // fusion: 144 -> 108 (pad 112) -> 72 (pad 80) -> 72 (pad 80)   (model_utils.py:141-163)
   UMT_TRY(add_tail_conv(m, folded_padded(t, fu + "0", fu + "1", 108, 144, 1, true, 112, 144), true, false));
@@ -576,6 +407,18 @@ int tail_forward(umt_model* m, int head, const float* feats, const float* intrin
                  float* out_scale, float* out_sigma, cudaStream_t st) {
   (void)n_img;
   const int B = n_samples;
+  if (B <= tail_fused_max_samples()) {   // small batches (per-frame tracker, time scan): one CTA per sample
+    const float* skel = nullptr;
+    if (head == UMT_HEAD_KNOWN_SKELETON) {
+      skeleton_kernel<<<n_skel, 144, 0, st>>>(skel_axes, skel_rest, m->tw.skel_w, m->tw.skel_b, m->tail_skel);
+      UMT_TRY(check_launch("skeleton_kernel"));
+      ++m->launches;
+      skel = m->tail_skel;
+    }
+    return tail_fused_forward(m, head, feats, intrinsics, extrinsics, sample_range, memory_idx, use_memory, hand_idx, B,
+                              skel, n_skel, mem_state, prev_extr, n_slots, out_joint_angles, out_wrist, out_scale,
+                              out_sigma, st);
+  }
   const FlatTensor &T0 = m->tail_flat[0], &T1 = m->tail_flat[1], &T2 = m->tail_flat[2];
   const TailWeights& tw = m->tw;
   fuse_prepare_kernel<<<B, 128, 0, st>>>(feats, intrinsics, extrinsics, sample_range, T0);
