@@ -222,7 +222,7 @@ def test_fp16_mode_refuses_weights_and_reports_activations_outside_the_half_rang
 
 
 def test_fused_small_batch_tail_and_tensor_core_tail_agree(monkeypatch):
-    """Batches up to 256 samples run the tail as one CTA per sample (csrc/tail_fused.cu, float32 FMAs);
+    """Batches up to 128 samples run the tail as one CTA per sample (csrc/tail_fused.cu, float32 FMAs);
     larger ones through the tensor-core convolutions of csrc/tail.cu.  Same inputs, same recurrent state:
     both within the keypoint gate of the oracle and within 1e-3 mm of each other, over three steps with
     mixed 1/2-view samples and memory resets."""
@@ -230,7 +230,7 @@ def test_fused_small_batch_tail_and_tensor_core_tail_agree(monkeypatch):
     hm = hmod.load_hand_model_from_dict(hm_dict())
     ax, rest = hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None]
     results = {}
-    for name, limit in (("fused", "256"), ("tensor", "0")):
+    for name, limit in (("fused", "128"), ("tensor", "0")):
         monkeypatch.setenv("UMT_TAIL_FUSED_MAX", limit)
         model = UmeTrackModel(sd).to("cuda")
         orc = O.OracleModel(sd)

@@ -1,8 +1,13 @@
 // The whole tail of ONE hand-frame in ONE CTA, for small batches: the per-frame tracker and the time
-// scan of the batched driver run the tail on 1-32 samples per step, where the fourteen launches of
-// tail.cu (ten of them tensor-core convolutions on a few hundred positions) are pure launch latency
-// (0.13 ms per step).  Here a sample's activations never leave shared memory and the convolutions are
-// plain float32 FMAs on the CUDA cores (19 MFLOP per sample: ~45 us on one SM), one launch per step.
+// scan of the batched driver run the tail on 1-32 samples per step, where the fifteen launches of
+// tail.cu (ten of them tensor-core convolutions on a few hundred positions) are launch latency
+// (0.17 ms per step, 34 ms of host time per 256-step scan).  Here a sample's activations never leave
+// shared memory and the convolutions are plain float32 FMAs on the CUDA cores: two launches per step
+// (skeleton encoder + this kernel).  Measured on B200 (UMT_TAIL_DBG=1): 278 k cycles per sample, of which
+// the four 3x3 regressor convolutions are 202 k -- 7.5 M FMAs on one SM's FP32 pipes (three-register FFMA
+// issues every other cycle per scheduler: 64 FMA/clk), i.e. the kernel is FP32-issue bound at 0.16 ms,
+// on par with the 15-launch path in device time and 7x cheaper on the host.  Splitting a sample over a
+// cluster of CTAs is the next step if the scan has to get faster.
 //   feature-transform layer + two-view fusion   lib/models/feature_extractor.py:61-141,
 //                                                lib/models/model_utils.py:57-104,141-192
 //   temporal memory (SimpleConvRNN)              lib/models/temporal.py:51-139
@@ -10,6 +15,7 @@
 //   world-space recovery / right-hand un-mirror  lib/models/umetrack_model.py:77-97
 // Arithmetic: float32 products and sums like the reference (no operand splitting needed on this path);
 // results agree with the tensor-core tail to ~1e-6 relative.
+#include <cstdio>
 #include <string>
 
 #include "model.cuh"
@@ -34,15 +40,28 @@ __device__ __forceinline__ void conv1x1_cta(const float* __restrict__ in, int ci
 #pragma unroll
     for (int i = 0; i < 18; ++i) acc[i] = b;
     const float* ip = in + 18 * g;
-#pragma unroll 2
-    for (int ci = 0; ci < cin; ++ci) {
-      const float wv = __ldg(w + (size_t)ci * cout + co);
-      const float2* row = reinterpret_cast<const float2*>(ip + ci * kPix);
+    // every layer's input width is a multiple of 18: fetch 18 weights at once (independent loads in flight;
+    // a single weight load per iteration made the loop pure L2 latency)
+    float wn[18];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) {
-        const float2 v = row[i];
-        acc[2 * i] = fmaf(wv, v.x, acc[2 * i]);
-        acc[2 * i + 1] = fmaf(wv, v.y, acc[2 * i + 1]);
+    for (int k = 0; k < 18; ++k) wn[k] = __ldg(w + (size_t)k * cout + co);
+    for (int c0 = 0; c0 < cin; c0 += 18) {
+      float wv[18];
+#pragma unroll
+      for (int k = 0; k < 18; ++k) wv[k] = wn[k];
+      if (c0 + 18 < cin) {
+#pragma unroll
+        for (int k = 0; k < 18; ++k) wn[k] = __ldg(w + (size_t)(c0 + 18 + k) * cout + co);
+      }
+#pragma unroll
+      for (int k = 0; k < 18; ++k) {
+        const float2* row = reinterpret_cast<const float2*>(ip + (c0 + k) * kPix);
+#pragma unroll
+        for (int i = 0; i < 9; ++i) {
+          const float2 v = row[i];
+          acc[2 * i] = fmaf(wv[k], v.x, acc[2 * i]);
+          acc[2 * i + 1] = fmaf(wv[k], v.y, acc[2 * i + 1]);
+        }
       }
     }
 #pragma unroll
@@ -64,7 +83,21 @@ __device__ __forceinline__ void conv3x3_cta(const float* __restrict__ in, float*
     for (int y = 0; y < 2; ++y)
 #pragma unroll
       for (int x = 0; x < 6; ++x) acc[y][x] = b;
+    // weights are requested three input channels ahead (an L2 round trip is ~3 iterations of this loop)
+    float wq[3][9];
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+#pragma unroll
+      for (int k = 0; k < 9; ++k) wq[d][k] = (d < c) ? __ldg(w + ((size_t)d * 9 + k) * c + co) : 0.f;
     for (int ci = 0; ci < c; ++ci) {
+      float wc[9];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { wc[k] = wq[0][k]; wq[0][k] = wq[1][k]; wq[1][k] = wq[2][k]; }
+      if (ci + 3 < c) {
+        const float* wp = w + (size_t)(ci + 3) * 9 * c + co;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) wq[2][k] = __ldg(wp + k * c);
+      }
       float win[4][8];
       const float4* src = reinterpret_cast<const float4*>(in + ci * kPad + 2 * g * 8);
 #pragma unroll
@@ -73,12 +106,11 @@ __device__ __forceinline__ void conv3x3_cta(const float* __restrict__ in, float*
         win[r][0] = lo.x; win[r][1] = lo.y; win[r][2] = lo.z; win[r][3] = lo.w;
         win[r][4] = hi.x; win[r][5] = hi.y; win[r][6] = hi.z; win[r][7] = hi.w;
       }
-      const float* wp = w + (size_t)ci * 9 * c + co;
 #pragma unroll
       for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
-          const float wv = __ldg(wp + (ky * 3 + kx) * c);
+          const float wv = wc[ky * 3 + kx];
 #pragma unroll
           for (int y = 0; y < 2; ++y)
 #pragma unroll
@@ -107,6 +139,7 @@ struct FusedParams {
   const float *fus_w[3], *fus_b[3], *tmp_w[3], *tmp_b[3], *reg_w[4], *reg_b[4], *head_w, *head_b;
   float *out_angles, *out_wrist, *out_scale, *out_sigma;
   unsigned* status;
+  int dbg;   // UMT_TAIL_DBG: block 0 prints the cycles of its phases
 };
 
 __global__ void __launch_bounds__(kFusedThreads)
@@ -128,6 +161,10 @@ tail_fused_kernel(const FusedParams P) {
   const bool multi = (r1 - r0) == 2;
   const int slot = (int)P.memory_idx[b];
   const bool slot_ok = slot >= 0 && slot < P.n_slots;
+  long long tk[8];
+  int nk = 0;
+  auto tick = [&]() { if (P.dbg && nk < 8) tk[nk++] = clock64(); };
+  tick();
 
   // ---- transforms (feature_extractor.py:61-87, model_utils.py:166-192, temporal.py:59-69) ----
   if (tid < 2 && multi) {
@@ -165,6 +202,7 @@ tail_fused_kernel(const FusedParams P) {
     sUse = use;
   }
   __syncthreads();
+  tick();
 
   // ---- two-view fusion (feature_extractor.py:121-133) or the single view's features ----
   if (multi) {
@@ -187,6 +225,7 @@ tail_fused_kernel(const FusedParams P) {
     for (int i = tid; i < 72 * kPix; i += kFusedThreads) B[i] = src[i];
   }
   __syncthreads();
+  tick();
 
   // ---- temporal input: [warped memory (18) | features in cam0 (72)] (temporal.py:65-85) ----
   {
@@ -211,6 +250,7 @@ tail_fused_kernel(const FusedParams P) {
   __syncthreads();
   conv1x1_cta(A, 90, B, 90, P.tmp_w[2], P.tmp_b[2], false);
   __syncthreads();
+  tick();
 
   // ---- memory write-back, regressor input [72 features | 4 skeleton] as a zero-bordered map ----
   if (slot_ok) {
@@ -231,6 +271,7 @@ tail_fused_kernel(const FusedParams P) {
   for (int i = tid; i < 76 * kPad; i += kFusedThreads) R1[i] = 0.f;       // (B is dead now)
   __syncthreads();
 
+  tick();
   // ---- two BasicBlocks (backbone_resnet.py:56-72) ----
   conv3x3_cta(R2, R0, P.c, P.reg_w[0], P.reg_b[0], nullptr);
   __syncthreads();
@@ -240,6 +281,7 @@ tail_fused_kernel(const FusedParams P) {
   __syncthreads();
   conv3x3_cta(R0, R2, P.c, P.reg_w[3], P.reg_b[3], R1);
   __syncthreads();
+  tick();
 
   // ---- average pool, 1x1 head (they commute), decoders ----
   if (tid < 80) {
@@ -257,14 +299,20 @@ tail_fused_kernel(const FusedParams P) {
   __syncthreads();
   head_decode(tid, sRaw, b, P.head == UMT_HEAD_UNKNOWN_SKELETON ? 1 : 0, P.extrinsics, P.sample_range, P.hand_idx,
               P.out_angles, P.out_wrist, P.out_scale, P.out_sigma);
+  if (P.dbg) {
+    __syncthreads();
+    tick();
+    if (b == 0 && tid == 0)
+      printf("tail_fused cycles: transforms %lld, fusion %lld, temporal %lld, pack %lld, regressor %lld, head %lld\n",
+             tk[1] - tk[0], tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[6] - tk[5]);
+  }
 }
 
-// Largest batch that takes this path (UMT_TAIL_FUSED_MAX overrides; 0 switches it off).  Beyond it the
-// tensor-core tail of tail.cu is used: on 2048 samples both cost about the same, and the split-bf16
-// convolutions there are what the large-batch parity tests pin.
+// Largest batch that takes this path (UMT_TAIL_FUSED_MAX overrides; 0 switches it off).  Beyond one wave
+// of CTAs the tensor-core tail of tail.cu is faster (256 samples: 0.18 ms against 0.25 ms).
 int tail_fused_max_samples() {
   const char* e = getenv("UMT_TAIL_FUSED_MAX");
-  return e ? atoi(e) : 256;
+  return e ? atoi(e) : 128;   // up to one CTA per SM: a single wave
 }
 
 int tail_fused_forward(umt_model* m, int head, const float* feats, const float* intrinsics,
@@ -285,6 +333,7 @@ int tail_fused_forward(umt_model* m, int head, const float* feats, const float* 
   p.head_w = tw.head_w[head]; p.head_b = tw.head_b[head];
   p.out_angles = out_joint_angles; p.out_wrist = out_wrist; p.out_scale = out_scale; p.out_sigma = out_sigma;
   p.status = m->d_status;
+  p.dbg = getenv("UMT_TAIL_DBG") ? 1 : 0;
   {  // opt-in shared-memory size: once per device
     static bool done[64] = {};
     int dev = 0;
