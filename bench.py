@@ -294,7 +294,7 @@ def recordings_sharded(model, hm_dict, dev, rank, world, n_rec, n_frames, group=
     import torch.distributed as dist
 
     from umetrack_b200 import synthetic
-    from umetrack_b200.batched import track_recordings_batched
+    from umetrack_b200.batched import label_arrays, track_recordings_batched
     from umetrack_b200.metrics import MetricSums, shard_indices
 
     H, W4 = 480, 2560
@@ -308,6 +308,7 @@ def recordings_sharded(model, hm_dict, dev, rank, world, n_rec, n_frames, group=
     def recording(r):
         if r not in labels_of:
             labels_of[r] = synthetic.make_recording(hm_dict, seed=r, n_frames=n_frames, with_frames=False)[0]
+            label_arrays(labels_of[r])        # JSON lists -> arrays once, like parsing the label file
         return labels_of[r], frames_of(r)
 
     def run(indices, sums, staged=None):

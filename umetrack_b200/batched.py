@@ -17,6 +17,7 @@ memory iff it was tracked in the previous frame; a frame without any hand resets
 """
 from __future__ import annotations
 
+import collections
 import ctypes
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -34,6 +35,32 @@ from .skinning import fk_landmarks_device
 
 
 _NEUTRAL_CACHE: Dict[tuple, torch.Tensor] = {}
+
+
+_LABEL_KEYS = ("joint_angles", "wrist_transforms", "hand_confidences", "camera_to_world_transforms", "camera_angles")
+_LABEL_CACHE: "collections.OrderedDict" = collections.OrderedDict()
+
+
+def label_arrays(labels: dict) -> dict:
+    """The per-frame label lists of a recording (lib/tracker/video_pose_data.py:75-93: nested Python lists
+    out of the JSON) as numpy arrays.  Converted once per set of list objects (the cache keeps the lists
+    alive, so their identities stay valid) -- list -> array conversion was a fifth of the batched driver's
+    host time.  Replacing a list in the dict (e.g. new confidences) gives a new entry; edits INSIDE a list
+    that was already used are not seen (treat label lists as immutable)."""
+    src = tuple(labels[k] for k in _LABEL_KEYS)
+    key = tuple(id(v) for v in src)
+    hit = _LABEL_CACHE.get(key)
+    if hit is not None:
+        _LABEL_CACHE.move_to_end(key)
+        return hit[1]
+    arr = {"joint_angles": np.asarray(src[0], dtype=np.float32), "wrist_transforms": np.asarray(src[1], dtype=np.float32),
+           "hand_confidences": np.asarray(src[2], dtype=np.float64),
+           "camera_to_world_transforms": np.asarray(src[3], dtype=np.float64),
+           "camera_angles": np.asarray(src[4], dtype=np.float64)}
+    _LABEL_CACHE[key] = (src, arr)
+    while len(_LABEL_CACHE) > 256:
+        _LABEL_CACHE.popitem(last=False)
+    return arr
 
 
 def crop_cameras_raw(hand_model: HandModel, ja: torch.Tensor, wr: torch.Tensor, is_right: torch.Tensor,
@@ -92,9 +119,10 @@ def crop_cameras_device(hand_model: HandModel, labels: dict, device: torch.devic
     sel_count [T,2], sel_cam [T,2,2], resample_params [T,2,2,48] f64, intrinsics [T,2,2,3,3],
     extrinsics [T,2,2,4,4]; hands with fewer than `min_num_crops` views get sel_count 0."""
     cams = labels["cameras"]
-    ja = torch.tensor(np.asarray(labels["joint_angles"]), dtype=torch.float32, device=device)          # [T,2,22]
-    wr = torch.tensor(np.asarray(labels["wrist_transforms"]), dtype=torch.float32, device=device)      # [T,2,4,4]
-    conf = np.asarray(labels["hand_confidences"], dtype=np.float64)                                    # [T,2]
+    arr = label_arrays(labels)
+    ja = torch.from_numpy(arr["joint_angles"]).to(device)               # [T,2,22] (float32 like perspective_crop.py:32-36)
+    wr = torch.from_numpy(arr["wrist_transforms"]).to(device)           # [T,2,4,4]
+    conf = arr["hand_confidences"]                                      # [T,2]
     T = ja.shape[0]
     n = T * 2
     mirror = torch.tensor([0, 1], dtype=torch.uint8, device=device).repeat(T)                          # hand index
@@ -102,8 +130,8 @@ def crop_cameras_device(hand_model: HandModel, labels: dict, device: torch.devic
     frame_idx = torch.arange(T, dtype=torch.int32, device=device).repeat_interleave(2)
     intr = torch.tensor([[c["fx"], c["fy"], c["cx"], c["cy"]] + [c[k] for k in FISHEYE62_FIELDS] for c in cams],
                         dtype=torch.float64, device=device)
-    c2w = torch.tensor(np.asarray(labels["camera_to_world_transforms"]), dtype=torch.float64, device=device).contiguous()
-    angles = torch.tensor(labels["camera_angles"], dtype=torch.float64, device=device)
+    c2w = torch.from_numpy(arr["camera_to_world_transforms"]).to(device).contiguous()
+    angles = torch.from_numpy(arr["camera_angles"]).to(device)
     r = crop_cameras_raw(hand_model, ja.reshape(n, 22), wr.reshape(n, 4, 4), mirror, valid, frame_idx, intr, c2w,
                          angles, int(cams[0]["ImageSizeX"]), int(cams[0]["ImageSizeY"]), opts)
     check_crop_camera_error(int(r["err"].item()))
@@ -234,8 +262,9 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
         T = counts[r].shape[0]
         mirror = torch.tensor([0] * T + [1] * T, dtype=torch.uint8, device=dev)
         pred = fk_landmarks_device(hm, out_ja[r].reshape(-1, 22), out_wr[r].reshape(-1, 4, 4), mirror)
-        gja = torch.tensor(np.asarray(lab["joint_angles"]), dtype=torch.float32, device=dev).permute(1, 0, 2)
-        gwr = torch.tensor(np.asarray(lab["wrist_transforms"]), dtype=torch.float32, device=dev).permute(1, 0, 2, 3)
+        arr = label_arrays(lab)
+        gja = torch.from_numpy(arr["joint_angles"]).to(dev).permute(1, 0, 2)
+        gwr = torch.from_numpy(arr["wrist_transforms"]).to(dev).permute(1, 0, 2, 3)
         gt = fk_landmarks_device(hm, gja.reshape(-1, 22).contiguous(), gwr.reshape(-1, 4, 4).contiguous(), mirror)
         v = torch.from_numpy(valid[r].reshape(-1)).to(dev)
         if sums is not None:
