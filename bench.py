@@ -282,13 +282,14 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
-def recordings_sharded(model, hm_dict, dev, rank, world, n_rec, n_frames, group=8):
+def recordings_sharded(model, hm_dict, dev, rank, world, n_rec, n_frames, group=64):
     """BASELINE configs[4]: `n_rec` synthetic recordings (seeds 0..n_rec-1, `n_frames` frames, 4 fisheye
     views, both hands, dropouts) sharded by recording over the ranks (longest-processing-time first),
     every rank running the batched driver on its shard -- crop cameras, resampling, encoder, time
     scan, FK, MPJPE / acceleration sums -- and ONE all-reduce of the metric sums at the end
     (run_eval_known_skeleton.py:113-119 is a Pool(8).map over recordings followed by a concatenate).
-    Frames are seeded noise generated on the device ("decoded frames staged to the GPU"); labels are
+    Up to `group` recordings of a rank are tracked together (one resampling launch, one encoder batch, ONE time
+    scan whose steps carry the hands of all of them).  Frames are seeded noise generated on the device ("decoded frames staged to the GPU"); labels are
     the reference's JSON schema.  Returns the stage record; collective: every rank must call it."""
     import torch
     import torch.distributed as dist
