@@ -212,6 +212,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     int kb = 0;
     long long w_bempty = 0;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      if (P.b_resident && tile != (int)blockIdx.x) break;   // resident weights: loaded with the first tile only
       int k = 0;
       for (int i = 0; i < P.n_stages; ++i) {
         const int nt = P.st_ntaps[i];
@@ -275,7 +276,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
           const int n = min(G, nt - t0);
           const int bslot = kb % n_b;
           c0 = P.dbg ? clock64() : 0;
-          mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          if (!P.b_resident || tile == (int)blockIdx.x) mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
           if (P.dbg) w_b += clock64() - c0;
           tc_fence_after();
           const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
@@ -287,7 +288,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
               case 2: issue_taps<2, COUT, SPLIT, MERGE>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
               default: issue_taps<4, COUT, SPLIT, MERGE>(P, i, t0, n, a_lo32, a_hi32, a_plane_bytes, b_lo32, b_hi32, d_base, idesc, any, skip_hilo); break;
             }
-            if (cl == 1) tc_commit(b_empty(bslot));
+            if (P.b_resident) {}                                  // resident weights are never released
+            else if (cl == 1) tc_commit(b_empty(bslot));
             else tc_commit_multicast(b_empty(bslot), cta_mask);   // frees the slot in every CTA of the cluster
           }
           any = 1u;
@@ -1405,6 +1407,21 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   long long nb = ((long long)budget - (long long)fixed - (long long)(a * n_a)) / (long long)b;
   p.n_a = n_a;
   p.n_b = (int)std::max(3LL, std::min((long long)env_int("UMT_CONV_NB_MAX", 24), nb));
+  p.b_resident = 0;
+  // Narrow layers: the whole weight set is a few tens of KB.  If it fits beside three A stages, every CTA
+  // loads it once and keeps it -- no weight pipeline, no per-stage hand-shake, more room for A stages
+  // (UMT_CONV_RESIDENT=0 switches this off).
+  if (env_int("UMT_CONV_RESIDENT", 1) && L.cout <= 64) {
+    int groups = 0;
+    for (int i = 0; i < p.n_stages; ++i) groups += (p.st_ntaps[i] + 8) / 9;
+    const size_t need = fixed + a * 3 + (size_t)groups * 9 * slab;
+    if (need <= budget && 2 * 3 + 2 * groups + 4 <= 120) {
+      p.b_resident = 1;
+      p.bgroup = 9;
+      p.n_b = groups;
+      p.n_a = 3 + (int)std::min<size_t>(3, (budget - need) / a);
+    }
+  }
 }
 
 int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, float* features,

@@ -50,6 +50,7 @@ struct ConvParams {
   int halo_rows;            // hi_shift - lo_shift
   int n_a, n_b;             // pipeline depths (A patches, B slabs)
   int bgroup;               // weight slabs (taps) per B pipeline stage
+  int b_resident;           // 1: the layer's weights fit: every CTA loads them once and keeps them (n_b = stages per tile)
   int n_buf;                // TMEM accumulator buffers (1 or 2)
   int cluster;              // CTAs per cluster sharing (multicasting) the weight slabs
   int occ;                  // CTAs per SM the grid is sized for
