@@ -1155,7 +1155,10 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     for (int i = 0; i < ns - p.res_stages; ++i) ntaps.push_back(p.st_ntaps[i]);
     for (int kind = 0; kind < 3; ++kind) {
       L.pair_G[kind] = (kind == 0 || L.cout == 256) ? 3 : 9;
-      if (const char* e = getenv(kind == 0 ? "UMT_PAIR_G_SPLIT" : "UMT_PAIR_G16")) { const int g = atoi(e); if (g == 1 || g == 3 || g == 9) L.pair_G[kind] = g; }
+      const std::string gname = std::string(kind == 0 ? "UMT_PAIR_G_SPLIT" : "UMT_PAIR_G16") + std::to_string(L.cout);
+      const char* e = getenv(gname.c_str());
+      if (!e) e = getenv(kind == 0 ? "UMT_PAIR_G_SPLIT" : "UMT_PAIR_G16");
+      if (e) { const int g = atoi(e); if (g == 1 || g == 3 || g == 9) L.pair_G[kind] = g; }
       std::vector<uint16_t> pb;
       pack_pair_blob(blob, L.cout, ntaps, L.pair_G[kind], kind, f2h, bf2f, pb);
       UMT_CUDA_TRY(cudaMalloc(&L.d_pair[kind], pb.size() * 2));
