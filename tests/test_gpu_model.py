@@ -230,8 +230,9 @@ def test_fused_small_batch_tail_and_tensor_core_tail_agree(monkeypatch):
     hm = hmod.load_hand_model_from_dict(hm_dict())
     ax, rest = hm.joint_rotation_axes.float()[None], (hm.joint_rest_positions * 1e-3).float()[None]
     results = {}
-    for name, limit in (("fused", "128"), ("tensor", "0")):
+    for name, limit, cluster in (("cluster", "128", "4096"), ("fused", "128", "0"), ("tensor", "0", "0")):
         monkeypatch.setenv("UMT_TAIL_FUSED_MAX", limit)
+        monkeypatch.setenv("UMT_TAIL_CLUSTER_MAX", cluster)     # a sample per CTA cluster / per CTA
         model = UmeTrackModel(sd).to("cuda")
         orc = O.OracleModel(sd)
         kps, launches = [], []
@@ -260,4 +261,7 @@ def test_fused_small_batch_tail_and_tensor_core_tail_agree(monkeypatch):
             assert np.abs(out.skel_scales.cpu().numpy() - g[f"u_scales_{step}"]).max() < 2e-5
             assert np.abs(out.wrist_xfs.cpu().numpy() - g[f"u_wrist_xfs_{step}"]).max() < 2e-5
     assert float((results["fused"][0] - results["tensor"][0]).abs().max()) < 1e-3
+    # the cluster variant deals the same per-element FMA chains to eight CTAs: bit-identical keypoints
+    assert torch.equal(results["cluster"][0], results["fused"][0])
+    assert results["cluster"][1] == results["fused"][1]
     assert results["fused"][1][0] == 26 + 2 and results["tensor"][1][0] == 26 + 15     # launches per forward pass

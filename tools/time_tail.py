@@ -1,5 +1,5 @@
 """Device time of one tail step (fusion + temporal + regressor + head) on small batches, fused
-one-CTA-per-sample kernel against the tensor-core tail (GPU box):  python tools/time_tail.py [bs ...]"""
+one-CTA-per-sample kernel and its cluster variant against the tensor-core tail (GPU box):  python tools/time_tail.py [bs ...]"""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -18,8 +18,9 @@ for bs in [int(a) for a in sys.argv[1:]] or [2, 16, 64, 256]:
     n_steps = 200
     ax = skel.joint_rotation_axes.expand(bs, 22, 3).contiguous()
     rs = skel.joint_rest_positions.expand(bs, 22, 3).contiguous()
-    for limit in ("0", "4096"):
+    for name, limit, cl in (("tensor ", "0", "0"), ("fused  ", "4096", "0"), ("cluster", "4096", "4096")):
         os.environ["UMT_TAIL_FUSED_MAX"] = limit
+        os.environ["UMT_TAIL_CLUSTER_MAX"] = cl
 
         def scan():   # one C call stepping the same rows n_steps times: no Python between the steps
             model.tail_scan(feats, d["intrinsics"], d["extrinsics_xf"], [(0, bs)] * n_steps, d["sample_range"],
@@ -30,4 +31,4 @@ for bs in [int(a) for a in sys.argv[1:]] or [2, 16, 64, 256]:
         e0.record()
         scan()
         e1.record(); torch.cuda.synchronize()
-        print(f"bs {bs:4d} {'fused ' if limit != '0' else 'tensor'}: {e0.elapsed_time(e1) / n_steps * 1e3:8.1f} us per step", flush=True)
+        print(f"bs {bs:4d} {name}: {e0.elapsed_time(e1) / n_steps * 1e3:8.1f} us per step", flush=True)

@@ -92,6 +92,14 @@ struct Folded {           // conv weight with BatchNorm folded in: w[co][ci][ks*
   int cout, cin, ks;
 };
 
+// Cluster variant of the fused small-batch tail (tail_fused.cu): a sample is spread over kClusterCtas CTAs,
+// CTA r owns ceil(cout / kClusterCtas) <= kSliceStride output channels of every layer; its packed slice is
+// [rows][kSliceStride] weights + [kSliceStride] biases (rows = cin, x 9 taps for a 3x3 layer; a constant row
+// stride keeps the kernel's shared-memory offsets compile-time constants).
+constexpr int kClusterCtas = 8;
+constexpr int kSliceStride = 16;
+__host__ __device__ constexpr int cluster_slice_floats(int rows) { return (rows + 1) * kSliceStride; }
+
 struct TailWeights {
   // BatchNorm-folded float32 weights, device pointers
   float *proj_w, *proj_b;                 // [256,72] (transposed), [72]: CUDA-core projection (UMT_PROJ_SIMT=1)
@@ -102,6 +110,7 @@ struct TailWeights {
   float *fus_w[3], *fus_b[3];             // fusion 144->108->72->72 (BN folded)
   float *tmp_w[3], *tmp_b[3];             // temporal 90->90 x3
   float *reg_w[2][4], *reg_b[2][4];       // regressor_k (C = 76) / regressor_u (C = 72): four 3x3 convs (BN folded)
+  float *fus_cl[3], *tmp_cl[3], *reg_cl[2][4];   // the same, packed per CTA of the cluster variant (tail_fused.cu)
   uint8_t *stem_pack_bf, *stem_pack_h16;  // tensor-core stem operand [hi|lo][2][128][8] bf16 / [2][128][8] fp16
 };
 

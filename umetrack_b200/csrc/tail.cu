@@ -302,6 +302,23 @@ static float* upload_ci_major(umt_model* m, const Folded& f) {
   return upload(m, w);
 }
 
+// The same weights packed per CTA of the cluster variant: slice r = [cin*kk][16] (zero beyond its channels), [16] biases.
+static float* upload_cluster_slices(umt_model* m, const Folded& f) {
+  const int kk = f.ks * f.ks, rows = f.cin * kk, per = (f.cout + kClusterCtas - 1) / kClusterCtas;
+  const int n = cluster_slice_floats(rows);
+  std::vector<float> w((size_t)kClusterCtas * n, 0.f);
+  for (int r = 0; r < kClusterCtas; ++r)
+    for (int j = 0; j < per; ++j) {
+      const int co = r * per + j;
+      if (co >= f.cout) break;
+      float* dst = w.data() + (size_t)r * n;
+      for (int ci = 0; ci < f.cin; ++ci)
+        for (int k = 0; k < kk; ++k) dst[(size_t)(ci * kk + k) * kSliceStride + j] = f.w[((size_t)co * f.cin + ci) * kk + k];
+      dst[(size_t)rows * kSliceStride + j] = f.b[co];
+    }
+  return upload(m, w);
+}
+
 int tail_build(umt_model* m, const float* const* t) {
   m->tail_convs.clear();
   {  // unpadded float32 copies for the fused small-batch kernel
@@ -312,10 +329,14 @@ int tail_build(umt_model* m, const float* const* t) {
     for (int i = 0; i < 3; ++i) {
       m->tw.fus_w[i] = upload_ci_major(m, f[i]);
       m->tw.fus_b[i] = upload(m, f[i].b);
+      m->tw.fus_cl[i] = upload_cluster_slices(m, f[i]);
       const Folded g = folded_padded(t, te + std::to_string(2 * i), "", 90, 90, 1, true, 90, 90);
       m->tw.tmp_w[i] = upload_ci_major(m, g);
       m->tw.tmp_b[i] = upload(m, g.b);
-      if (!m->tw.fus_w[i] || !m->tw.fus_b[i] || !m->tw.tmp_w[i] || !m->tw.tmp_b[i]) return UMT_ERR_CUDA;
+      m->tw.tmp_cl[i] = upload_cluster_slices(m, g);
+      if (!m->tw.fus_w[i] || !m->tw.fus_b[i] || !m->tw.tmp_w[i] || !m->tw.tmp_b[i] || !m->tw.fus_cl[i] ||
+          !m->tw.tmp_cl[i])
+        return UMT_ERR_CUDA;
     }
     const char* heads[2] = {"_regressor_k", "_regressor_u"};
     const int hc[2] = {76, 72};
@@ -326,7 +347,8 @@ int tail_build(umt_model* m, const float* const* t) {
         const Folded g = folded_padded(t, pre + cv, pre + bn, hc[h], hc[h], 3, false, hc[h], hc[h]);
         m->tw.reg_w[h][c] = upload_ci_major(m, g);
         m->tw.reg_b[h][c] = upload(m, g.b);
-        if (!m->tw.reg_w[h][c] || !m->tw.reg_b[h][c]) return UMT_ERR_CUDA;
+        m->tw.reg_cl[h][c] = upload_cluster_slices(m, g);
+        if (!m->tw.reg_w[h][c] || !m->tw.reg_b[h][c] || !m->tw.reg_cl[h][c]) return UMT_ERR_CUDA;
       }
   }
   const std::string fu = "_feature_extractor._multi_view_fusion.";
