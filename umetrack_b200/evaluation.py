@@ -70,19 +70,24 @@ def track_recording(model, labels: dict, frames: np.ndarray, hand_model: Optiona
     gtk = np.zeros([NUM_HANDS, T, NUM_LANDMARKS_PER_HAND, 3])
     valid = np.zeros([NUM_HANDS, T], dtype=bool)
     tracker = tracker or HandTracker(model, HandTrackerOpts())
+    # The reference computes the landmarks of the tracked and the ground-truth pose inside the loop
+    # (run_eval_known_skeleton.py:70-81).  They do not feed back into the tracking, so here the poses are
+    # collected and both landmark sets come from one FK launch each after the loop (same kernel, same
+    # per-pose arithmetic; two device->host reads per recording instead of two per frame).
+    items, ja_p, wr_p, ja_g, wr_g = [], [], [], [], []
     for t, (frame, gt) in enumerate(stream):
         cc = tracker.gen_crop_cameras([v.camera for v in frame.views], stream.camera_angles,
                                       stream.hand_model, gt, min_num_crops=1)
         res = tracker.track_frame(frame, pred_model, cc)
-        hands = sorted(res.hand_poses.keys())
-        if not hands:
-            continue
-        ja = np.stack([res.hand_poses[h].joint_angles for h in hands] + [gt[h].joint_angles for h in hands])
-        wr = np.stack([res.hand_poses[h].wrist_xform for h in hands] + [gt[h].wrist_xform for h in hands])
-        n = len(hands)
-        lm_pred = landmarks_from_poses(pred_model, ja[:n], wr[:n], hands)
-        lm_gt = landmarks_from_poses(stream.hand_model, ja[n:], wr[n:], hands)
-        for k, h in enumerate(hands):
+        for h in sorted(res.hand_poses.keys()):
+            items.append((h, t))
+            ja_p.append(res.hand_poses[h].joint_angles); wr_p.append(res.hand_poses[h].wrist_xform)
+            ja_g.append(gt[h].joint_angles); wr_g.append(gt[h].wrist_xform)
+    if items:
+        hands_all = [h for h, _ in items]
+        lm_pred = landmarks_from_poses(pred_model, np.stack(ja_p), np.stack(wr_p), hands_all)
+        lm_gt = landmarks_from_poses(stream.hand_model, np.stack(ja_g), np.stack(wr_g), hands_all)
+        for k, (h, t) in enumerate(items):
             tracked[h, t], gtk[h, t], valid[h, t] = lm_pred[k], lm_gt[k], True
     dev = sums.device if sums is not None else torch.device("cuda", torch.cuda.current_device())
     p = torch.from_numpy(tracked.reshape(-1, 21, 3)).float().to(dev)

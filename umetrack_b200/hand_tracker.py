@@ -153,6 +153,63 @@ def warp_views_device(views: List[ViewData], pairs: List[Tuple[int, PinholePlane
     return (out_f, out_u) if want_u8 else out_f
 
 
+_NP2T = {np.float64: torch.float64, np.float32: torch.float32, np.int64: torch.int64, np.int32: torch.int32,
+         np.uint8: torch.uint8, np.bool_: torch.bool}
+
+
+class _Section:
+    """One pinned host buffer, one device buffer of the same layout, and typed views of both."""
+
+    def __init__(self, device: torch.device, spec):
+        off, self.offsets = 0, {}
+        for name, dt, shape in spec:
+            self.offsets[name] = off
+            off += (int(np.prod(shape)) * np.dtype(dt).itemsize + 15) & ~15
+        self.nbytes = off
+        self.host = torch.zeros(off, dtype=torch.uint8).pin_memory()
+        self.dev = torch.zeros(off, dtype=torch.uint8, device=device)
+        raw = self.host.numpy()
+        self.h, self.d = {}, {}
+        for name, dt, shape in spec:
+            o, nb = self.offsets[name], int(np.prod(shape)) * np.dtype(dt).itemsize
+            self.h[name] = raw[o:o + nb].view(dt).reshape(shape)
+            self.d[name] = self.dev[o:o + nb].view(_NP2T[dt]).view(shape)
+
+    def upload(self, nbytes: Optional[int] = None):
+        n = self.nbytes if nbytes is None else nbytes
+        self.dev[:n].copy_(self.host[:n], non_blocking=True)
+
+    def download(self):
+        self.host.copy_(self.dev, non_blocking=True)
+
+
+class _FrameBuffers:
+    """Persistent buffers of the per-frame path for one rig (n_cam views of h x w pixels): every
+    frame rewrites them in place, so a frame costs two host->device copies, two device->host copies
+    and no allocation, and the CUDA graph of the forward pass reads its inputs where they are
+    (InputFrameDesc.persistent_inputs)."""
+
+    def __init__(self, device: torch.device, n_cam: int, h: int, w: int, n_pose: int):
+        H, C = NUM_HANDS, NUM_HANDS * MAX_VIEW_NUM
+        self.key = (n_cam, h, w, n_pose)
+        self.crop_in = _Section(device, [
+            ("intr", np.float64, (n_cam, 12)), ("c2w", np.float64, (n_cam, 16)), ("angles", np.float64, (n_cam,)),
+            ("poses", np.float32, (H, n_pose, 22)), ("wrists", np.float32, (H, n_pose, 16)),
+            ("mirror", np.uint8, (H, n_pose)), ("is_right", np.uint8, (H,)), ("valid", np.uint8, (H,)),
+            ("frame_idx", np.int32, (H,))])
+        self.crop_in.h["valid"][:] = 1
+        self.crop_out = _Section(device, [
+            ("err", np.int32, (4,)), ("sel_count", np.int32, (H,)), ("sel_cam", np.int32, (H, MAX_VIEW_NUM)),
+            ("params", np.float64, (H, MAX_VIEW_NUM, 48)), ("intr", np.float32, (H, MAX_VIEW_NUM, 9)),
+            ("extr", np.float32, (H, MAX_VIEW_NUM, 16))])
+        self.points = torch.zeros((H, n_pose * 21, 3), dtype=torch.float32, device=device)
+        self.frame_in = _Section(device, [
+            ("intr", np.float32, (C, 3, 3)), ("extr", np.float32, (C, 4, 4)), ("range", np.int64, (H, 2)),
+            ("hand", np.int64, (H,)), ("use_memory", np.bool_, (H,)), ("offsets", np.int64, (C,)),
+            ("params", np.float64, (C, 48)), ("images", np.uint8, (n_cam, h, w))])
+        self.crops = torch.zeros((C, 96, 96), dtype=torch.float32, device=device)
+
+
 class HandTracker:
     def __init__(self, model, opts: HandTrackerOpts) -> None:
         if not torch.cuda.device_count():
@@ -170,6 +227,10 @@ class HandTracker:
         self.use_cuda_graphs = True           # replay the per-frame forward pass as one CUDA graph (same results)
         self._skel_cache = None
         self._last_hands = None
+        self._fb: Optional[_FrameBuffers] = None      # persistent buffers of the per-frame path
+        self._crop_cache = None                       # device-side results of the last gen_crop_cameras
+        self._fb_model_key = None
+        self._result_pin: Optional[torch.Tensor] = None   # pinned copy of the model's packed outputs
 
     def _graph_scope(self):
         import contextlib
@@ -204,40 +265,77 @@ class HandTracker:
                 out[hand_idx] = per_hand
         return out
 
-    def _gen_crop_cameras_device(self, cameras, camera_angles, hand_model: HandModel, hands, min_num_crops: int):
-        from .batched import check_crop_camera_error, crop_cameras_raw
+    def _buffers(self, n_cam: int, h: int, w: int) -> _FrameBuffers:
+        n_pose = self._num_crop_points // 21
+        if self._fb is None or self._fb.key != (n_cam, h, w, n_pose):
+            self._fb = _FrameBuffers(self._device, n_cam, h, w, n_pose)
+            self._fb_model_key = None
+        return self._fb
 
-        dev, n, n_cam = self._device, len(hands), len(cameras)
-        # one upload: [intr n_cam*12 | camera_to_world n_cam*16 | angles n_cam | joint angles n*22 | wrists n*16]
-        host = np.concatenate([
-            np.array([[*c.f, *c.c, *c.distort_coeffs] for c in cameras], dtype=np.float64).reshape(-1),
-            np.stack([np.asarray(c.camera_to_world_xf, dtype=np.float64) for c in cameras]).reshape(-1),
-            np.asarray(camera_angles, dtype=np.float64).reshape(-1),
-            np.stack([np.asarray(p.joint_angles, dtype=np.float32) for _, p in hands]).astype(np.float64).reshape(-1),
-            np.stack([np.asarray(p.wrist_xform, dtype=np.float32) for _, p in hands]).astype(np.float64).reshape(-1)])
-        buf = torch.from_numpy(host).to(dev)
-        o = np.cumsum([0, n_cam * 12, n_cam * 16, n_cam, n * 22, n * 16])
-        is_right = torch.tensor([1 if h == RIGHT_HAND_INDEX else 0 for h, _ in hands], dtype=torch.uint8, device=dev)
-        opts = HandTrackerOpts(num_crop_points=self._num_crop_points, hand_ratio_in_crop=self._hand_ratio_in_crop,
-                               min_required_vis_landmarks=self._min_required_vis_landmarks)
-        r = crop_cameras_raw(
-            hand_model, buf[o[3]:o[4]].reshape(n, 22).float(), buf[o[4]:o[5]].reshape(n, 4, 4).float(), is_right,
-            torch.ones(n, dtype=torch.uint8, device=dev), torch.zeros(n, dtype=torch.int32, device=dev),
-            buf[o[0]:o[1]].reshape(n_cam, 12), buf[o[1]:o[2]].reshape(1, n_cam, 4, 4), buf[o[2]:o[3]],
-            cameras[0].width, cameras[0].height, opts)
-        back = torch.cat([r["err"].double(), r["sel_count"].double(), r["sel_cam"].reshape(-1).double(),
-                          r["resample_params"][:, :, 28:48].reshape(-1)]).cpu().numpy()     # one read
-        check_crop_camera_error(int(back[0]))
-        cnt, sel = back[1:1 + n].astype(int), back[1 + n:1 + 3 * n].astype(int).reshape(n, 2)
-        par = back[1 + 3 * n:].reshape(n, 2, 20)
+    def _gen_crop_cameras_device(self, cameras, camera_angles, hand_model: HandModel, hands, min_num_crops: int):
+        """All hands of the frame in two launches (landmark FK of the given / neutral / open pose, then
+        umt_crop_cameras), one upload and one read, through the persistent buffers.  The device-side
+        rows (resampling parameters, model intrinsics / extrinsics) are kept for track_frame."""
+        from .batched import check_crop_camera_error
+        from .skinning import _device_model
+
+        n, n_cam = len(hands), len(cameras)
+        fb = self._buffers(n_cam, int(cameras[0].height), int(cameras[0].width))
+        n_pose = fb.key[3]
+        ci, co = fb.crop_in, fb.crop_out
+        hv = ci.h
+        lim = hand_model.joint_limits
+        mkey = (lim.data_ptr(), lim._version)
+        if self._fb_model_key != mkey:          # pose slots 1 (neutral) and 2 (open = zeros) change with the hand model only
+            hv["poses"][:] = 0
+            if n_pose > 1:
+                hv["poses"][:, 1] = neutral_joint_angles(hand_model).numpy()
+            self._fb_model_key = mkey
+        hv["intr"][:] = [[*c.f, *c.c, *c.distort_coeffs] for c in cameras]
+        hv["c2w"][:] = [np.asarray(c.camera_to_world_xf, dtype=np.float64).reshape(16) for c in cameras]
+        hv["angles"][:] = camera_angles
+        for i, (h, p) in enumerate(hands):
+            hv["poses"][i, 0] = p.joint_angles
+            hv["wrists"][i] = np.asarray(p.wrist_xform, dtype=np.float32).reshape(16)
+            hv["is_right"][i] = hv["mirror"][i] = 1 if h == RIGHT_HAND_INDEX else 0
+        ci.upload()
+        co.dev.zero_()
+        lib = native.lib()
+        stream = native.current_stream_ptr()
+        dv = ci.d
+        axes, rest, lm_rest, lm_idx, lm_w = _device_model(hand_model, self._device)
+        with torch.cuda.device(self._device):
+            native.check(lib.umt_fk_landmarks(
+                native.ptr(axes), native.ptr(rest), native.ptr(lm_rest), native.ptr(lm_idx), native.ptr(lm_w),
+                native.ptr(dv["poses"]), native.ptr(dv["wrists"]), native.ptr(dv["mirror"]), n * n_pose,
+                native.ptr(fb.points), stream), "umt_fk_landmarks")
+            od = co.d
+            native.check(lib.umt_crop_cameras(
+                native.ptr(fb.points), native.ptr(dv["frame_idx"]), native.ptr(dv["is_right"]), native.ptr(dv["valid"]),
+                native.ptr(dv["intr"]), native.ptr(dv["c2w"]), native.ptr(dv["angles"]), n_cam,
+                int(cameras[0].width), int(cameras[0].height), n, n_pose * 21, self._min_required_vis_landmarks,
+                float(self._hand_ratio_in_crop), native.ptr(od["sel_count"]), native.ptr(od["sel_cam"]),
+                native.ptr(od["params"]), native.ptr(od["intr"]), native.ptr(od["extr"]), native.ptr(od["err"]),
+                stream), "umt_crop_cameras")
+        co.download()
+        torch.cuda.current_stream().synchronize()
+        oh = co.h
+        check_crop_camera_error(int(oh["err"][0]))
+        cnt, sel = oh["sel_count"][:n].copy(), oh["sel_cam"][:n].copy()
+        rows = {"params": oh["params"][:n].copy(), "intr": oh["intr"][:n].copy(), "extr": oh["extr"][:n].copy()}
         out: Dict[int, Dict[int, PinholePlaneCameraModel]] = {}
+        index = {}
         for i, (hand_idx, _) in enumerate(hands):
+            par = rows["params"][i, :, 28:48]
             per_hand = {int(sel[i, k]): PinholePlaneCameraModel(
-                width=int(self._input_size[0]), height=int(self._input_size[1]), f=par[i, k, 0:2].copy(),
-                c=par[i, k, 2:4].copy(), distort_coeffs=(), camera_to_world_xf=par[i, k, 4:20].reshape(4, 4).copy())
+                width=int(self._input_size[0]), height=int(self._input_size[1]), f=par[k, 0:2].copy(),
+                c=par[k, 2:4].copy(), distort_coeffs=(), camera_to_world_xf=par[k, 4:20].reshape(4, 4).copy())
                 for k in range(int(cnt[i]))}
             if per_hand and len(per_hand) >= min_num_crops:
                 out[hand_idx] = per_hand
+                index[hand_idx] = i
+        self._crop_cache = {"out": out, "index": index, "rows": rows, "views": [id(c) for c in cameras],
+                            "sig": tuple((h, tuple(v.keys())) for h, v in out.items())}
         return out
 
     def track_frame(self, sample: InputFrame, hand_model: HandModel, crop_cameras) -> TrackingResult:
@@ -258,7 +356,71 @@ class HandTracker:
             out = self._model.regress_pose_pred_skel_scale(data, desc)
             return self._gen_tracking_result(out, self._last_hands, crop_cameras)
 
+    def _skeleton(self, hand_model_mm: Optional[HandModel]):
+        if hand_model_mm is None:
+            return None
+        # the metre-scaled skeleton is rebuilt when the hand model's tensors change (also in place)
+        key = tuple((t.data_ptr(), t._version) for t in (hand_model_mm.joint_rotation_axes,
+                                                        hand_model_mm.joint_rest_positions))
+        if self._skel_cache is None or self._skel_cache[0] != key:
+            hm = scaled_hand_model(hand_model_mm, MM_TO_M)
+            self._skel_cache = (key, InputSkeletonData(
+                joint_rotation_axes=hm.joint_rotation_axes.float().to(self._device).contiguous(),
+                joint_rest_positions=hm.joint_rest_positions.float().to(self._device).contiguous()))
+        return self._skel_cache[1]
+
+    def _make_inputs_persistent(self, sample: InputFrame, hand_model_mm: Optional[HandModel], crop_cameras, cache):
+        """`_make_inputs` when `crop_cameras` is what the last gen_crop_cameras call returned: the
+        model's camera matrices and the resampling rows are the ones umt_crop_cameras wrote (the
+        numbers the host construction would give, lib/tracker/tracker.py:188-236), everything goes
+        up in one copy, and the crops are written into the buffer the CUDA graph reads."""
+        fb, rows = self._fb, cache["rows"]
+        fi = fb.frame_in
+        hv = fi.h
+        views = sample.views
+        h, w = fb.key[1], fb.key[2]
+        slot: Dict[int, int] = {}
+        n = bs = 0
+        hands = []
+        for hand_idx, per_hand in crop_cameras.items():
+            i, start = cache["index"][hand_idx], n
+            for k, cam_idx in enumerate(per_hand.keys()):
+                if cam_idx not in slot:
+                    img = views[cam_idx].image
+                    if img.shape != (h, w):
+                        raise ValueError("all views of a frame must have the same size")
+                    slot[cam_idx] = len(slot)
+                    hv["images"][slot[cam_idx]] = img
+                hv["intr"][n] = rows["intr"][i, k].reshape(3, 3)
+                hv["extr"][n] = rows["extr"][i, k].reshape(4, 4)
+                hv["params"][n] = rows["params"][i, k]
+                hv["offsets"][n] = slot[cam_idx] * h * w
+                n += 1
+            hv["range"][bs] = (start, n)
+            hv["hand"][bs] = hand_idx
+            hv["use_memory"][bs] = self._valid_tracking_history[hand_idx]
+            hands.append(hand_idx)
+            bs += 1
+        fi.upload(fi.offsets["images"] + len(slot) * h * w)
+        dv = fi.d
+        with torch.cuda.device(self._device):
+            native.check(native.lib().umt_resample_crops(
+                native.ptr(dv["images"]), native.ptr(dv["offsets"]), w, w, h, native.ptr(dv["params"]), n, 0,
+                native.ptr(fb.crops), 0, native.current_stream_ptr()), "umt_resample_crops")
+        data = InputFrameData(left_images=fb.crops[:n], intrinsics=dv["intr"][:n], extrinsics_xf=dv["extr"][:n])
+        desc = InputFrameDesc(sample_range=dv["range"][:bs], memory_idx=dv["hand"][:bs],
+                              use_memory=dv["use_memory"][:bs], hand_idx=dv["hand"][:bs],
+                              n_memory_slots=NUM_HANDS, persistent_inputs=True)
+        self._last_hands = np.array(hands)
+        return data, desc, self._skeleton(hand_model_mm)
+
     def _make_inputs(self, sample: InputFrame, hand_model_mm: Optional[HandModel], crop_cameras):
+        cache = self._crop_cache
+        if (cache is not None and cache["out"] is crop_cameras and self._fb is not None
+                and cache["sig"] == tuple((h, tuple(v.keys())) for h, v in crop_cameras.items())
+                and len(sample.views) == self._fb.key[0]
+                and all(isinstance(v.image, np.ndarray) and v.image.dtype == np.uint8 for v in sample.views)):
+            return self._make_inputs_persistent(sample, hand_model_mm, crop_cameras, cache)
         pairs, intr, extr, ranges, hands = [], [], [], [], []
         for hand_idx, per_hand in crop_cameras.items():
             start = len(pairs)
@@ -289,30 +451,33 @@ class HandTracker:
             use_memory=torch.from_numpy(self._valid_tracking_history[hands_np]).to(dev),
             hand_idx=ints_d[2 * bs:],
             n_memory_slots=NUM_HANDS)        # memory_idx is a hand index: the bank always has both slots
-        skel = None
-        if hand_model_mm is not None:
-            # the metre-scaled skeleton is rebuilt when the hand model's tensors change (also in place)
-            key = tuple((t.data_ptr(), t._version) for t in (hand_model_mm.joint_rotation_axes,
-                                                            hand_model_mm.joint_rest_positions))
-            if self._skel_cache is None or self._skel_cache[0] != key:
-                hm = scaled_hand_model(hand_model_mm, MM_TO_M)
-                self._skel_cache = (key, InputSkeletonData(
-                    joint_rotation_axes=hm.joint_rotation_axes.float().to(dev),
-                    joint_rest_positions=hm.joint_rest_positions.float().to(dev)))
-            skel = self._skel_cache[1]
         self._last_hands = hands_np
-        return data, desc, skel
+        return data, desc, self._skeleton(hand_model_mm)
 
     def _gen_tracking_result(self, out: RegressorOutput, hand_indices: np.ndarray, crop_cameras) -> TrackingResult:
         n = out.joint_angles.shape[0]
-        parts = [out.joint_angles.reshape(n, 22), out.wrist_xfs.reshape(n, 16)]
-        if out.skel_scales is not None:
-            parts.append(out.skel_scales.reshape(n, 1))
-        back = torch.cat(parts, dim=1).to("cpu").numpy()            # one device->host read per frame
-        ja = np.ascontiguousarray(back[:, :22])
-        wr = np.ascontiguousarray(back[:, 22:38]).reshape(n, 4, 4)
+        packed = getattr(self._model, "_last_packed", None)
+        if packed is not None and packed[0].data_ptr() == out.joint_angles.data_ptr():
+            # outputs of a CUDA-graph replay: slices of one buffer, read with one copy into pinned memory
+            buf, (_, o_wr, _, o_sc) = packed
+            pin = self._result_pin
+            if pin is None or pin.numel() < buf.numel():
+                pin = self._result_pin = torch.empty(max(buf.numel(), 256), dtype=torch.float32).pin_memory()
+            pin[:buf.numel()].copy_(buf, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            back = pin.numpy()
+            ja = back[:n * 22].reshape(n, 22).copy()
+            wr = back[o_wr:o_wr + n * 16].reshape(n, 4, 4).copy()
+            scales = None if out.skel_scales is None else back[o_sc:o_sc + n].copy()
+        else:
+            parts = [out.joint_angles.reshape(n, 22), out.wrist_xfs.reshape(n, 16)]
+            if out.skel_scales is not None:
+                parts.append(out.skel_scales.reshape(n, 1))
+            back = torch.cat(parts, dim=1).to("cpu").numpy()            # one device->host read per frame
+            ja = np.ascontiguousarray(back[:, :22])
+            wr = np.ascontiguousarray(back[:, 22:38]).reshape(n, 4, 4)
+            scales = None if out.skel_scales is None else np.ascontiguousarray(back[:, 38])
         wr[..., :3, 3] *= M_TO_MM
-        scales = None if out.skel_scales is None else np.ascontiguousarray(back[:, 38])
         poses, n_views, pred_scales = {}, {}, {}
         for i, h in enumerate(hand_indices):
             h = int(h)

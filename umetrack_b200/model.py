@@ -44,13 +44,19 @@ class InputFrameDesc:
     it.  The reference reads `max(memory_idx) + 1` on the host at every call to grow its memory bank
     (lib/models/temporal.py:101-123); with the promise the bank is sized without that device->host
     read.  A broken promise does not corrupt memory: the sample runs without recurrent memory and
-    UMT_STATUS_MEMORY_INDEX is raised by `UmeTrackModel.check_status()`."""
+    UMT_STATUS_MEMORY_INDEX is raised by `UmeTrackModel.check_status()`.
+
+    `persistent_inputs` is a second extension for per-frame callers: the promise that the image,
+    camera and descriptor tensors of this call are the same device buffers at every call of this
+    shape (the caller rewrites them in place between calls).  A CUDA-graph replay then reads them
+    where they are instead of copying nine small tensors into buffers of its own."""
 
     sample_range: torch.Tensor
     memory_idx: torch.Tensor
     use_memory: torch.Tensor
     hand_idx: torch.Tensor
     n_memory_slots: Optional[int] = None
+    persistent_inputs: bool = False
 
 
 @dataclass
@@ -112,6 +118,7 @@ class UmeTrackModel:
         self.last_launch_count = 0
         self._frame_graphs = False
         self._graphs: Dict[tuple, dict] = {}
+        self._last_packed = None     # (buffer, offsets) of the last graph replay's outputs, else None
 
     # ---- nn.Module-like surface the callers use ----------------------------------------------
     def eval(self):
@@ -282,7 +289,9 @@ class UmeTrackModel:
         self._grow_memory(need)
         dev = self._device
         if (self._frame_graphs and features is None and n_img <= 8 and (skel is not None or head == native.HEAD_UNKNOWN)):
-            return self._forward_graph(head, images, intr, extr, srange, mem_idx, use_mem, hand_idx, skel)
+            return self._forward_graph(head, images, intr, extr, srange, mem_idx, use_mem, hand_idx, skel,
+                                       persistent=bool(frame_desc.persistent_inputs))
+        self._last_packed = None
         ja = torch.empty((bs, 22), dtype=torch.float32, device=dev)
         wr = torch.empty((bs, 4, 4), dtype=torch.float32, device=dev)
         sg = torch.empty((bs, 21), dtype=torch.float32, device=dev)
@@ -315,8 +324,10 @@ class UmeTrackModel:
         self.last_launch_count = lib.umt_model_last_launch_count(self._handle)
         return RegressorOutput(joint_angles=ja, wrist_xfs=wr, skel_scales=sc, landmark_uncertainty_sigmas=sg)
 
-    def _forward_graph(self, head, images, intr, extr, srange, mem_idx, use_mem, hand_idx, skel) -> RegressorOutput:
-        """Replay (or capture) the CUDA graph of umt_model_forward for this shape."""
+    def _forward_graph(self, head, images, intr, extr, srange, mem_idx, use_mem, hand_idx, skel,
+                       persistent: bool = False) -> RegressorOutput:
+        """Replay (or capture) the CUDA graph of umt_model_forward for this shape.  The outputs are
+        slices of one buffer (`_last_packed`), so that a per-frame caller reads them with one copy."""
         dev = self._device
         n_img, bs = images.shape[0], srange.shape[0]
         axes = rest = None
@@ -324,18 +335,21 @@ class UmeTrackModel:
             axes = self._prep(skel.joint_rotation_axes, torch.float32).reshape(-1, 22, 3)
             rest = self._prep(skel.joint_rest_positions, torch.float32).reshape(-1, 22, 3)
         n_skel = 0 if axes is None else axes.shape[0]
-        key = (head, self._mode, n_img, bs, n_skel, images.dtype, self._ws.data_ptr(), self._mem_features.data_ptr(),
-               len(self._mem_features))
-        g = self._graphs.get(key)
         ins = [images, intr, extr, srange, mem_idx, use_mem, hand_idx] + ([axes, rest] if axes is not None else [])
+        key = (head, self._mode, n_img, bs, n_skel, images.dtype, self._ws.data_ptr(), self._mem_features.data_ptr(),
+               len(self._mem_features), tuple(t.data_ptr() for t in ins) if persistent else None)
+        g = self._graphs.get(key)
         if g is None:
             if len(self._graphs) > 16:
                 self._graphs.clear()
-            st = [t.clone() for t in ins]
-            out = {"ja": torch.empty((bs, 22), dtype=torch.float32, device=dev),
-                   "wr": torch.empty((bs, 4, 4), dtype=torch.float32, device=dev),
-                   "sg": torch.empty((bs, 21), dtype=torch.float32, device=dev),
-                   "sc": torch.empty((bs,), dtype=torch.float32, device=dev) if head == native.HEAD_UNKNOWN else None}
+            st = ins if persistent else [t.clone() for t in ins]
+            r4 = lambda v: (v + 3) & ~3          # every output starts on a 16-byte boundary
+            o_wr, o_sg, o_sc = r4(bs * 22), r4(bs * 22) + bs * 16, r4(r4(bs * 22) + bs * 16 + bs * 21)
+            pack = torch.empty(o_sc + r4(bs), dtype=torch.float32, device=dev)
+            out = {"ja": pack[:bs * 22].view(bs, 22), "wr": pack[o_wr:o_wr + bs * 16].view(bs, 4, 4),
+                   "sg": pack[o_sg:o_sg + bs * 21].view(bs, 21),
+                   "sc": pack[o_sc:o_sc + bs] if head == native.HEAD_UNKNOWN else None,
+                   "pack": pack, "offsets": (0, o_wr, o_sg, o_sc)}
             lib = native.lib()
             fwd = lib.umt_model_forward_u8 if images.dtype == torch.uint8 else lib.umt_model_forward
 
@@ -361,12 +375,13 @@ class UmeTrackModel:
                     call()
             g = {"graph": graph, "st": st, "out": out, "launches": native.lib().umt_model_last_launch_count(self._handle)}
             self._graphs[key] = g
-        else:
+        elif not persistent:
             for dst, src in zip(g["st"], ins):
                 dst.copy_(src)
         g["graph"].replay()
         self.last_launch_count = g["launches"]
         o = g["out"]
+        self._last_packed = (o["pack"], o["offsets"])
         return RegressorOutput(joint_angles=o["ja"], wrist_xfs=o["wr"], skel_scales=o["sc"],
                                landmark_uncertainty_sigmas=o["sg"])
 
