@@ -56,6 +56,7 @@ struct alignas(64) PairParams {
   int guard[2], planes[2];  // guard rows / hi planes (C/8) of the two sources
   int n_stages;
   int relu, res_epi, phase_out;
+  int overlap_launch;       // host only: launch with programmatic stream serialization
   uint8_t st_src[kPairMaxStages], st_chunk[kPairMaxStages], st_ntaps[kPairMaxStages];
   short tap_shift[kMaxTaps];
   uint8_t st_tap0[kPairMaxStages];
@@ -165,9 +166,11 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
   cluster_sync_all();   // the peer's barriers exist before anything is signalled across the pair
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) grid_launch_dependents();   // (after the TMEM allocation, see conv_umma_kernel)
 
   if (warp == 0 && lane == 0) {
     // ===== A-patch producer (both CTAs): own 128 positions + halo, one 16-channel slice per stage =====
+    grid_dependency_wait();     // the activations are the previous launch's output
     int it = 0;
     for (int tile = pair_id; tile < P.n_tiles; tile += n_pairs) {
       const long long q0 = ((long long)tile * 2 + rank) * (S * 128);
@@ -286,6 +289,7 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
     }
   } else if (warp >= 4) {
     // ===== epilogue (both CTAs): own 128 rows of the accumulator -> bias / residual / ReLU -> global =====
+    grid_dependency_wait();     // residual rows and the output tensor belong to earlier launches until they are done
     const int lgrp = warp & 3;
     int tc = 0;
     bool fp16_over = false;
@@ -470,7 +474,17 @@ static int launch_pair_s(const PairParams& p, cudaStream_t st) {
     }
   }
   const int pairs = std::max(1, std::min(p.n_tiles, pair_sm_count()));   // two CTAs per SM = one pair per SM on average
-  kernel<<<2 * pairs, kPairThreads, smem, st>>>(p);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)(2 * pairs));
+  cfg.blockDim = dim3(kPairThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.overlap_launch ? 1 : 0;      // (the cluster shape is a compile-time attribute of the kernel)
+  UMT_CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, p));
   return check_launch("conv_pair_kernel");
 }
 
@@ -538,6 +552,7 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
   }
   p.patch_rows = p.n_box * p.box_rows;
   p.relu = c.relu; p.res_epi = c.res_epi; p.phase_out = c.phase_out;
+  p.overlap_launch = c.overlap_launch;
   p.bias = c.bias;
   p.status = c.status;
   p.res = c.res;

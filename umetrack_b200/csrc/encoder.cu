@@ -148,6 +148,14 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   const uint32_t cl = (uint32_t)P.cluster;
   uint32_t cta_rank = 0;
   if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+  // output-channel slices (ConvParams::n_slices): this CTA's slice, and its place among the CTAs that walk tiles
+  const int n_sl = P.n_slices > 1 ? P.n_slices : 1;
+  const int slice = n_sl > 1 ? (int)blockIdx.x % n_sl : 0;
+  const int vblock = n_sl > 1 ? (int)blockIdx.x / n_sl : (int)blockIdx.x;
+  const int vgrid = n_sl > 1 ? (int)gridDim.x / n_sl : (int)gridDim.x;
+  const uint8_t* const weights = n_sl > 1 ? P.slice_weights[slice] : P.weights;
+  const float* const bias = n_sl > 1 ? P.slice_bias[slice] : P.bias;
+  const int pl0 = slice * (COUT / 8);      // first output / residual plane of the slice
   const uint16_t cta_mask = (uint16_t)((1u << cl) - 1u);
   const int mc = P.S * 128;
   const uint32_t buf_cols = (uint32_t)(P.S * kDCols);
@@ -169,19 +177,24 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   if (warp == 3) {
-    for (int c = lane; c < COUT; c += 32) s_bias[c] = P.bias[c];
+    for (int c = lane; c < COUT; c += 32) s_bias[c] = bias[c];
   }
   tc_fence_before();
   __syncthreads();
   if (cl > 1) cluster_sync_all();   // peers' barriers must be initialised before anything is multicast
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // The next layer may now set itself up and stream its weights while this one runs.  (Only after this
+  // CTA owns its TMEM columns: a dependent CTA that took them first would wait for this grid while this
+  // CTA waits for the columns.)
+  if (threadIdx.x == 0) grid_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     // ===== A-patch producer: one 16-channel slice (2 planes hi [+2 planes lo]) per stage =====
+    grid_dependency_wait();     // the activations are the previous launch's output
     int it = 0;
     long long w_aempty = 0, t_begin = clock64();
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+    for (int tile = vblock; tile < P.n_tiles; tile += vgrid) {
       const long long q0 = (long long)tile * mc;
       for (int i = 0; i < P.n_stages; ++i, ++it) {
         const int slot = it % n_a;
@@ -211,8 +224,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     // numeric mode is contiguous in program order)
     int kb = 0;
     long long w_bempty = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      if (P.b_resident && tile != (int)blockIdx.x) break;   // resident weights: loaded with the first tile only
+    for (int tile = vblock; tile < P.n_tiles; tile += vgrid) {
+      if (P.b_resident && tile != vblock) break;   // resident weights: loaded with the first tile only
       int k = 0;
       for (int i = 0; i < P.n_stages; ++i) {
         const int nt = P.st_ntaps[i];
@@ -225,7 +238,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
           const uint32_t bytes = (uint32_t)n * kBSlab;
           mbar_expect_tx(b_full(slot), bytes);
           const uint32_t dst = smem_u32(b_base + (size_t)slot * b_stage_bytes);
-          const uint8_t* src = P.weights + (size_t)k * kBSlab;
+          const uint8_t* src = weights + (size_t)k * kBSlab;
           if (cl == 1) {
             bulk_g2s(dst, src, bytes, b_full(slot));
           } else {
@@ -252,7 +265,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     long long w_acc = 0, w_a = 0, w_b = 0, t_begin = clock64();
     unsigned long long g_begin = 0;
     if (P.dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_begin));
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
+    for (int tile = vblock; tile < P.n_tiles; tile += vgrid, ++tc) {
       const int buf = tc % n_buf;
       long long c0 = P.dbg ? clock64() : 0;
       mbar_wait(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // epilogue drained this buffer
@@ -276,7 +289,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
           const int n = min(G, nt - t0);
           const int bslot = kb % n_b;
           c0 = P.dbg ? clock64() : 0;
-          if (!P.b_resident || tile == (int)blockIdx.x) mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          if (!P.b_resident || tile == vblock) mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
           if (P.dbg) w_b += clock64() - c0;
           tc_fence_after();
           const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
@@ -313,11 +326,12 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
     }
   } else if (warp >= 4) {
     // ===== epilogue: TMEM -> registers -> bias / ReLU -> split bf16 -> global =====
+    grid_dependency_wait();     // residual rows and the output tensor belong to earlier launches until they are done
     const int lgrp = warp & 3;  // TMEM lane group this warp may read
     int tc = 0;
     bool fp16_over = false;
     long long w_full = 0, t_begin = clock64();
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tc) {
+    for (int tile = vblock; tile < P.n_tiles; tile += vgrid, ++tc) {
       const int buf = tc % n_buf;
       const long long q0 = (long long)tile * mc;
       constexpr int kStep = (COUT % 32 == 0 && !MERGE) ? 32 : 16;   // columns per TMEM round trip
@@ -326,7 +340,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
       // processed (and the first chunk's before the accumulator is awaited)
       uint4 rn_h[kRows], rn_l[kRows];
       auto res_fetch = [&](long long q, bool valid, int c0) {
-        const uint8_t* g = P.res.base + (long long)(c0 >> 3) * P.res.plane_stride + (P.res.guard + q) * 16;
+        const uint8_t* g = P.res.base + (long long)(pl0 + (c0 >> 3)) * P.res.plane_stride + (P.res.guard + q) * 16;
 #pragma unroll
         for (int h = 0; h < kRows; ++h) {
           if (valid) {
@@ -342,7 +356,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
         // into L2 now (they were written two layers ago and have usually been evicted)
         if (q0 + (long long)P.S * 128 <= P.n_pos) {
           for (int s = 0; s < P.S; ++s) {
-            const uint8_t* g = P.res.base + (P.res.guard + q0 + s * 128 + lgrp * 32 + lane) * 16;
+            const uint8_t* g = P.res.base + (long long)pl0 * P.res.plane_stride + (P.res.guard + q0 + s * 128 + lgrp * 32 + lane) * 16;
 #pragma unroll 4
             for (int pl = 0; pl < COUT / 8; ++pl) {
               asm volatile("prefetch.global.L2 [%0];" ::"l"(g + (long long)pl * P.res.plane_stride));
@@ -412,7 +426,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
                   if (c < P.dense_c) P.dense_out[(img * P.dense_c + c) * hw + pix] = f[e];
                 }
               } else {
-                store_row8<MODE>(T, (c0 >> 3) + h, o.row, f);
+                store_row8<MODE>(T, pl0 + (c0 >> 3) + h, o.row, f);
               }
             }
           }
@@ -483,18 +497,21 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   }
   int grid = std::min(p.n_tiles, sm_count() * std::max(1, p.occ));
   grid = std::max(p.cluster, grid / p.cluster * p.cluster);
+  if (p.n_slices > 1) grid = p.n_tiles * p.n_slices;      // few tiles: one CTA per (tile, output-channel slice)
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)grid);
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = (unsigned)p.cluster;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = p.overlap_launch ? 2 : 1;
   UMT_CUDA_TRY(cudaLaunchKernelEx(&cfg, kernel, pd));
   return check_launch("conv_umma_kernel");
 }
@@ -1148,7 +1165,7 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
     m->owned.push_back(L.d_weights_h16);
     UMT_CUDA_TRY(cudaMemcpy(L.d_weights_h16, h1.data(), h1.size() * 2, cudaMemcpyHostToDevice));
   }
-  if (main.ks == 3 && L.stride == 1 && p.a_nsrc == 1 && (L.cout == 32 || L.cout == 64 || L.cout == 128 || L.cout == 256)) {
+  if (!L.no_pair && main.ks == 3 && L.stride == 1 && p.a_nsrc == 1 && (L.cout == 32 || L.cout == 64 || L.cout == 128 || L.cout == 256)) {
     // weights repacked per CTA half for the pair kernel (conv_pair.cu); the trailing identity stages are
     // not part of it (these widths always add the residual in the epilogue)
     std::vector<int> ntaps;
@@ -1179,6 +1196,39 @@ int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds)
   return UMT_OK;
 }
 
+// 128 / 256 output channels: the same layer once more as 2 / 4 layers of 64 output channels (own weight
+// blobs in every numeric mode, own biases), for launches on few positions -- a frame of the per-frame
+// tracker has one or two 128-position tiles in these layers, and a tile of the whole layer is 20-30 us of
+// tensor-core time on one SM; as (tile, slice) CTAs the layer spreads over 8-12 SMs (ConvParams::n_slices).
+static int build_slices(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds) {
+  constexpr int kSlice = 64;
+  L.slices.clear();
+  if (L.cout < 128 || L.cout % kSlice != 0 || L.cout / kSlice > 4 || !env_int("UMT_CONV_SLICES", 1)) return UMT_OK;
+  auto cut = [&](const Folded& f, int j) {
+    Folded g;
+    g.cout = kSlice; g.cin = f.cin; g.ks = f.ks;
+    const size_t row = (size_t)f.cin * f.ks * f.ks;
+    g.w.assign(f.w.begin() + (size_t)j * kSlice * row, f.w.begin() + (size_t)(j + 1) * kSlice * row);
+    g.b.assign(f.b.begin() + (size_t)j * kSlice, f.b.begin() + (size_t)(j + 1) * kSlice);
+    return g;
+  };
+  for (int j = 0; j < L.cout / kSlice; ++j) {
+    ConvLayer S;
+    S.cout = kSlice; S.cin = L.cin; S.stride = L.stride; S.geom = L.geom; S.ds_cin = L.ds_cin;
+    S.src_kind = L.src_kind; S.src_buf = L.src_buf; S.out_buf = L.out_buf; S.res_buf = L.res_buf;
+    S.phase_out = L.phase_out; S.relu = L.relu; S.no_pair = 1;
+    const Folded fj = cut(main, j);
+    if (ds) {
+      const Folded dj = cut(*ds, j);
+      UMT_TRY(build_conv(m, S, fj, &dj));
+    } else {
+      UMT_TRY(build_conv(m, S, fj, nullptr));
+    }
+    L.slices.push_back(S);
+  }
+  return UMT_OK;
+}
+
 int encoder_build(umt_model* m, const float* const* t) {
   const std::string bb = "_feature_extractor._image_backbone.0._layers.";
   m->convs.clear();
@@ -1195,6 +1245,7 @@ int encoder_build(umt_model* m, const float* const* t) {
       c1.src_kind = first_ds ? 1 : 0; c1.src_buf = cur; c1.out_buf = 2; c1.res_buf = -1;
       Folded f1 = folded_from(t, pre + ".conv1", pre + ".bn1", cout, c1.cin, 3, false);
       UMT_TRY(build_conv(m, c1, f1, nullptr));
+      UMT_TRY(build_slices(m, c1, f1, nullptr));
       m->convs.push_back(c1);
       c2.cout = cout; c2.cin = cout; c2.stride = 1; c2.geom = g; c2.src_kind = 0; c2.src_buf = 2;
       c2.phase_out = (last && g < 3) ? 1 : 0;
@@ -1205,11 +1256,13 @@ int encoder_build(umt_model* m, const float* const* t) {
         c2.out_buf = 0;
         Folded fd = folded_from(t, pre + ".downsample.0", pre + ".downsample.1", cout, cin, 1, false);
         UMT_TRY(build_conv(m, c2, f2, &fd));
+        UMT_TRY(build_slices(m, c2, f2, &fd));
         cur = 0;
       } else {
         c2.res_buf = cur;
         c2.out_buf = 1 - cur;
         UMT_TRY(build_conv(m, c2, f2, nullptr));
+        UMT_TRY(build_slices(m, c2, f2, nullptr));
         cur = 1 - cur;
       }
       m->convs.push_back(c2);
@@ -1341,8 +1394,9 @@ void encoder_bind(umt_model* m, uint8_t* base) {
 void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode);
 
 static void fill_tensors(const umt_model* m, const ConvLayer& L, int n_img, int mode,
-                         ConvParams& p) {
+                         ConvParams& p, int force_S = 0) {
   p = (L.has_prog16 && mode != UMT_MODE_FP32_EQUIV) ? L.prog16 : L.prog;
+  p.force_S = force_S;
   const int g = L.geom;
   if (L.src_kind == 1) {
     for (int ph = 0; ph < 4; ++ph) p.src[ph] = m->phase[g][ph];
@@ -1384,10 +1438,16 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   // tile shape per numeric mode.  The merged split form (issue_taps) keeps two accumulators per sub-tile;
   // for the 32-channel layers two buffers of S = 2 sub-tiles (epilogue overlapped inside the CTA) beat one
   // buffer of S = 4 by 28 % (tools/ab_conv.py, B200).  UMT_CONV_SPLIT_CFG<cout>="S,nbuf" overrides.
+  if (p.force_S > 0 && p.force_S < p.S) {
+    p.S = p.force_S;
+    p.patch_rows = p.S * 128 + p.halo_rows;
+    p.n_buf = (2 * p.S * L.cout * p.occ <= 512) ? 2 : 1;
+  }
   if (split && L.cout <= 64) {
     int S = (L.cout == 32) ? 2 : p.S, nbuf = 2;
     const std::string name = "UMT_CONV_SPLIT_CFG" + std::to_string(L.cout);
     if (const char* e = getenv(name.c_str())) sscanf(e, "%d,%d", &S, &nbuf);
+    if (p.force_S > 0) S = std::min(S, p.force_S);
     S = std::max(1, std::min(4, S));
     while (S > 1 && S * 2 * L.cout * p.occ > 512) S >>= 1;
     p.S = S;
@@ -1466,12 +1526,34 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
     stem_kernel<UMT_MODE_FP16><<<blocks, 256, 0, st>>>(images, n_img, m->tw.stem_w, m->tw.stem_b, m->buf[0][0]);
   UMT_TRY(check_launch("stem_kernel"));
   ++m->launches;
+  const int overlap_max = env_int("UMT_CONV_OVERLAP_MAX", 64);
+  const long long slice_rows = env_int("UMT_CONV_SLICE_ROWS", 2048);   // wide layers run sliced up to this many positions
   for (size_t i = 0; i < m->convs.size(); ++i) {
     if (stop_after_layer >= 0 && (int)i > stop_after_layer) return UMT_OK;
     ConvParams p;
-    fill_tensors(m, m->convs[i], n_img, mode, p);
+    const ConvLayer& L = m->convs[i];
+    const long long rows = (long long)n_img * (kStageHW[L.geom] + 1) * (kStageHW[L.geom] + 1);
+    if (!L.slices.empty() && rows <= slice_rows) {
+      // few positions: (tile, 64-channel slice) CTAs of the one-CTA kernel instead of whole-layer tiles
+      fill_tensors(m, L.slices[0], n_img, mode, p, 1);
+      p.pair_weights = nullptr;
+      p.cluster = 1;
+      p.n_slices = (int)L.slices.size();
+      for (int j = 0; j < p.n_slices; ++j) {
+        p.slice_weights[j] = mode == UMT_MODE_FP32_EQUIV ? L.slices[j].d_weights
+                             : mode == UMT_MODE_FP16   ? L.slices[j].d_weights_h16 : L.slices[j].d_weights_hi;
+        p.slice_bias[j] = L.slices[j].d_bias;
+      }
+      p.n_tiles = (p.n_pos + p.S * 128 - 1) / (p.S * 128);
+    } else {
+      fill_tensors(m, L, n_img, mode, p);
+    }
     if (ev) cudaEventRecord(ev[1 + i], st);
-    UMT_TRY(launch_conv(p, m->convs[i].cout, mode, st));
+    // Small batches (a frame of the per-frame tracker): a layer takes ~18 us of which most is set-up and
+    // the weight stream of one or two CTAs; launched as programmatic dependents, the layers overlap that
+    // part with their predecessors (UMT_CONV_OVERLAP_MAX = largest crop count that does, 0 = never).
+    p.overlap_launch = (!ev && n_img <= overlap_max) ? 1 : 0;
+    UMT_TRY(launch_conv(p, p.n_slices > 1 ? 64 : L.cout, mode, st));
     ++m->launches;
   }
   if (ev) cudaEventRecord(ev[1 + m->convs.size()], st);
@@ -1483,6 +1565,7 @@ int encoder_run_chunk(umt_model* m, int mode, const float* images, int n_img, fl
     p.n_pos = n_img * 49;
     p.dense_out = features;
     p.dense_c = 72;
+    p.overlap_launch = (!ev && n_img <= overlap_max) ? 1 : 0;
     finalize_conv_params(p, m->proj_conv, mode);
     UMT_TRY(launch_conv(p, 80, mode, st));
     ++m->launches;

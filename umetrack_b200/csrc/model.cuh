@@ -51,6 +51,14 @@ struct ConvParams {
   int n_a, n_b;             // pipeline depths (A patches, B slabs)
   int bgroup;               // weight slabs (taps) per B pipeline stage
   int b_resident;           // 1: the layer's weights fit: every CTA loads them once and keeps them (n_b = stages per tile)
+  int overlap_launch;       // 1: programmatic dependent launch (set-up and weight stream overlap the previous layer)
+  // Output-channel slices (few positions, wide layers): CTA b works on slice b % n_slices of tile
+  // b / n_slices; a slice is COUT channels of the layer with its own weight blob and bias, and writes /
+  // adds the planes [slice * COUT / 8, ...) of the output / residual tensor.  0 or 1: no slicing.
+  int n_slices;
+  int force_S;              // >0: at most this many sub-tiles per CTA (sliced launches want many small tiles)
+  const uint8_t* slice_weights[4];
+  const float* slice_bias[4];
   int n_buf;                // TMEM accumulator buffers (1 or 2)
   int cluster;              // CTAs per cluster sharing (multicasting) the weight slabs
   int occ;                  // CTAs per SM the grid is sized for
@@ -85,6 +93,9 @@ struct ConvLayer {
   ConvParams prog{};                              // program template (tensors filled per call)
   ConvParams prog16{};                            // stride-2 layers: stage table used by the 16-bit modes
   int has_prog16 = 0;
+  int no_pair = 0;                                // 1: no pair-kernel blobs (the slices below)
+  std::vector<ConvLayer> slices;                  // 128 / 256 channels: the same layer as 2 / 4 layers of 64 output
+                                                  // channels each, for launches on few positions (ConvParams::n_slices)
 };
 
 struct Folded {           // conv weight with BatchNorm folded in: w[co][ci][ks*ks], b[co]

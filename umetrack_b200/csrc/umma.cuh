@@ -145,4 +145,13 @@ __device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) {
 // float32 NCHW output (projection)
 constexpr int kEpiPlain = 0, kEpiResidual = 1, kEpiDense = 2;
 
+
+// Programmatic dependent launch: a kernel launched with the "programmatic stream serialization" attribute
+// may start while its predecessor in the stream is still running.  Everything that does not depend on the
+// predecessor's results (barrier and TMEM set-up, the weight stream) runs at once; a thread calls
+// grid_dependency_wait() before it touches memory the predecessor writes or still reads.  Without the
+// attribute both calls do nothing.
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 }  // namespace umt

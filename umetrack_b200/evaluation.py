@@ -9,6 +9,7 @@ are supplied as the label dict of lib/tracker/video_pose_data.py:75-93 plus raw 
 """
 from __future__ import annotations
 
+import copy as _copy
 from typing import Dict, Iterator, Optional, Tuple
 
 import numpy as np
@@ -35,6 +36,9 @@ class RecordingStream:
         self.camera_to_world = np.array(labels["camera_to_world_transforms"])
         self.frames = frames
         assert len(self.joint_angles) == len(frames)
+        # every frame's cameras are `camera.copy(camera_to_world_xf=...)` of the same four cameras: the
+        # copy's intrinsics are computed once here, a frame's camera is a shallow clone with its own pose
+        self._camera_copies = [c.copy() for c in self.cameras]
 
     def __len__(self):
         return len(self.frames)
@@ -50,8 +54,11 @@ class RecordingStream:
             mv = raw.reshape(raw.shape[0], n_cam, -1)
             if self.camera_to_world[t].sum() == 0:
                 assert not gt, "Cameras are not tracked, expecting no ground truth tracking!"
-            views = [ViewData(image=mv[:, c, :], camera=self.cameras[c].copy(camera_to_world_xf=self.camera_to_world[t, c]),
-                              camera_angle=self.camera_angles[c]) for c in range(n_cam)]
+            views = []
+            for c in range(n_cam):
+                cam = _copy.copy(self._camera_copies[c])
+                cam.camera_to_world_xf = self.camera_to_world[t, c]
+                views.append(ViewData(image=mv[:, c, :], camera=cam, camera_angle=self.camera_angles[c]))
             yield InputFrame(views=views), gt
 
 

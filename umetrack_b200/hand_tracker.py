@@ -230,7 +230,16 @@ class HandTracker:
         self._fb: Optional[_FrameBuffers] = None      # persistent buffers of the per-frame path
         self._crop_cache = None                       # device-side results of the last gen_crop_cameras
         self._fb_model_key = None
+        self._stream_obj = None
         self._result_pin: Optional[torch.Tensor] = None   # pinned copy of the model's packed outputs
+
+    def _sync(self):
+        """Wait for the current stream.  The Stream object is kept between frames (building one costs
+        ~20 us) and refreshed when the raw handle of the current stream changes."""
+        st = self._stream_obj
+        if st is None or st.cuda_stream != native.current_stream_ptr():
+            st = self._stream_obj = torch.cuda.current_stream()
+        st.synchronize()
 
     def _graph_scope(self):
         import contextlib
@@ -299,7 +308,6 @@ class HandTracker:
             hv["wrists"][i] = np.asarray(p.wrist_xform, dtype=np.float32).reshape(16)
             hv["is_right"][i] = hv["mirror"][i] = 1 if h == RIGHT_HAND_INDEX else 0
         ci.upload()
-        co.dev.zero_()
         lib = native.lib()
         stream = native.current_stream_ptr()
         dv = ci.d
@@ -318,9 +326,12 @@ class HandTracker:
                 native.ptr(od["params"]), native.ptr(od["intr"]), native.ptr(od["extr"]), native.ptr(od["err"]),
                 stream), "umt_crop_cameras")
         co.download()
-        torch.cuda.current_stream().synchronize()
+        self._sync()
         oh = co.h
-        check_crop_camera_error(int(oh["err"][0]))
+        if int(oh["err"][0]):        # the flag is only ever set by the kernel: clear it for the next frame
+            code = int(oh["err"][0])
+            co.dev.zero_()
+            check_crop_camera_error(code)
         cnt, sel = oh["sel_count"][:n].copy(), oh["sel_cam"][:n].copy()
         rows = {"params": oh["params"][:n].copy(), "intr": oh["intr"][:n].copy(), "extr": oh["extr"][:n].copy()}
         out: Dict[int, Dict[int, PinholePlaneCameraModel]] = {}
@@ -464,7 +475,7 @@ class HandTracker:
             if pin is None or pin.numel() < buf.numel():
                 pin = self._result_pin = torch.empty(max(buf.numel(), 256), dtype=torch.float32).pin_memory()
             pin[:buf.numel()].copy_(buf, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+            self._sync()
             back = pin.numpy()
             ja = back[:n * 22].reshape(n, 22).copy()
             wr = back[o_wr:o_wr + n * 16].reshape(n, 4, 4).copy()

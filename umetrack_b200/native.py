@@ -96,6 +96,12 @@ def ptr(t) -> int:
 
 
 def current_stream_ptr() -> int:
+    """cudaStream_t of torch's current stream on the current device (the raw getter: the Stream
+    object of torch.cuda.current_stream() costs ~20 us to build, which a per-frame caller pays
+    several times per frame)."""
     import torch
 
+    raw = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+    if raw is not None:
+        return raw(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
