@@ -214,18 +214,22 @@ def measure_stages(model, hm, hm_dict, dev, peaks):
     # the reference's own call pattern: one gen_crop_cameras + track_frame per frame (HandTracker)
     from umetrack_b200.evaluation import track_recording
     lab1, fr1 = synthetic.make_recording(hm_dict, seed=100, n_frames=48)
-    track_recording(model, lab1, fr1)      # warm-up
+    track_recording(model, lab1, fr1)      # warm-up (captures the CUDA graphs of the frame shapes)
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    r1 = track_recording(model, lab1, fr1)
-    torch.cuda.synchronize()
-    dt1 = time.perf_counter() - t0
+    dt1 = 1e9
+    for _ in range(3):
+        t0 = time.perf_counter()
+        r1 = track_recording(model, lab1, fr1)
+        torch.cuda.synchronize()
+        dt1 = min(dt1, time.perf_counter() - t0)
     n1 = int(r1["valid_tracking"].sum())
     out["per_frame_tracker"] = {"frames": 48, "hand_frames": n1, "wall_s": dt1, "ms_per_frame": dt1 / 48 * 1e3,
                                 "hand_frames_per_s": n1 / dt1,
-                                "note": "HandTracker.gen_crop_cameras + track_frame + FK per frame, as "
-                                        "run_eval_known_skeleton.py calls them (host float64 crop cameras, "
-                                        "~41 kernel launches per frame): latency bound"}
+                                "note": "HandTracker.gen_crop_cameras + track_frame per frame as run_eval_known_skeleton.py "
+                                        "calls them, host objects in and out (best of 3): per frame two launches + one read "
+                                        "for the crop cameras, then upload + resample + one CUDA-graph replay of the forward "
+                                        "pass (29 kernels, ~0.40 ms on the device for 2-4 crops) + one read; landmark FK of "
+                                        "all frames after the loop"}
     return out
 
 

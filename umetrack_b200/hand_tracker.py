@@ -229,7 +229,7 @@ class HandTracker:
         self._last_hands = None
         self._fb: Optional[_FrameBuffers] = None      # persistent buffers of the per-frame path
         self._crop_cache = None                       # device-side results of the last gen_crop_cameras
-        self._fb_model_key = None
+        self._fb_model_key = self._fb_intr_key = None
         self._stream_obj = None
         self._result_pin: Optional[torch.Tensor] = None   # pinned copy of the model's packed outputs
 
@@ -278,7 +278,7 @@ class HandTracker:
         n_pose = self._num_crop_points // 21
         if self._fb is None or self._fb.key != (n_cam, h, w, n_pose):
             self._fb = _FrameBuffers(self._device, n_cam, h, w, n_pose)
-            self._fb_model_key = None
+            self._fb_model_key = self._fb_intr_key = None
         return self._fb
 
     def _gen_crop_cameras_device(self, cameras, camera_angles, hand_model: HandModel, hands, min_num_crops: int):
@@ -300,7 +300,10 @@ class HandTracker:
             if n_pose > 1:
                 hv["poses"][:, 1] = neutral_joint_angles(hand_model).numpy()
             self._fb_model_key = mkey
-        hv["intr"][:] = [[*c.f, *c.c, *c.distort_coeffs] for c in cameras]
+        ikey = tuple((c.f, c.c, c.distort_coeffs) for c in cameras)      # compared by value: a few microseconds
+        if ikey != self._fb_intr_key:
+            hv["intr"][:] = [[*c.f, *c.c, *c.distort_coeffs] for c in cameras]
+            self._fb_intr_key = ikey
         hv["c2w"][:] = [np.asarray(c.camera_to_world_xf, dtype=np.float64).reshape(16) for c in cameras]
         hv["angles"][:] = camera_angles
         for i, (h, p) in enumerate(hands):
@@ -354,9 +357,17 @@ class HandTracker:
             self.reset_history()
             return TrackingResult()
         data, desc, skel = self._make_inputs(sample, hand_model, crop_cameras)
-        with self._graph_scope():      # one CUDA-graph replay per frame; outputs are read before returning
-            out = self._model.regress_pose_use_skeleton(data, desc, skel)
+        # one CUDA-graph replay per frame; the graph's static outputs are read before returning
+        m = self._model
+        prev = getattr(m, "_frame_graphs", None)
+        if prev is not None and self.use_cuda_graphs:
+            m._frame_graphs = True
+        try:
+            out = m.regress_pose_use_skeleton(data, desc, skel)
             return self._gen_tracking_result(out, self._last_hands, crop_cameras)
+        finally:
+            if prev is not None:
+                m._frame_graphs = prev
 
     def track_frame_and_calibrate_scale(self, sample: InputFrame, crop_cameras) -> TrackingResult:
         if not crop_cameras:
