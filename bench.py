@@ -383,6 +383,8 @@ def main():
     ap.add_argument("--no-stages", action="store_true", help="skip the per-stage and recording measurements")
     ap.add_argument("--sharded-recordings", type=int, default=64)
     ap.add_argument("--sharded-frames", type=int, default=256)
+    ap.add_argument("--settle", type=float, default=SETTLE_S,
+                    help="seconds of untimed steps before each mode's timed legs (0 for profiler runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -516,7 +518,7 @@ def main():
         # that `e2e` against `value` shows the cost of the copies and not which leg ran on the cooler chip.
         torch.cuda.synchronize()
         t_settle, settle_steps = time.time(), 0
-        while time.time() - t_settle < SETTLE_S:
+        while time.time() - t_settle < args.settle:
             device_step(fd, desc)
             torch.cuda.synchronize()
             settle_steps += 1
@@ -555,7 +557,7 @@ def main():
                                "memory steady state", "hand_frames_per_step_per_gpu": B, "crops_per_hand_frame": 2,
                    "crops_per_sec": 2 * value, "numeric_mode": args.mode,
                    "settle": "%d untimed steps (%.1f s) after the %d warm-up steps, before the timed legs" % (
-                       state.get("settle_steps", 0), SETTLE_S, W),
+                       state.get("settle_steps", 0), args.settle, W),
                    "l2": "inputs (151 MB of float32 crops at B=2048) and activations exceed the 126 MB L2; no flush",
                    "sharding": "independent batches per rank, NCCL all-reduce of metric sums only"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

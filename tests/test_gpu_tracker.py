@@ -123,3 +123,38 @@ def test_hand_set_changing_at_equal_size_matches_reference():
     assert np.abs(res["per_frame_mean_error"] - g["per_frame_error"]).max() < 0.01
     model.check_status()          # no memory index fell outside the bank
     assert len(model._mem_features) == 2
+
+
+def test_persistent_frame_path_equals_the_general_path():
+    """track_frame takes the persistent-buffer path (device-side camera rows, CUDA graph reading its
+    inputs in place, packed outputs) when it is handed gen_crop_cameras' own dict, and the general path
+    (camera matrices rebuilt on the host, separate uploads) for any other dict.  Same recording through
+    both: poses agree to float32 round-off of the camera matrices, and both use the recurrent memory."""
+    from umetrack_b200.evaluation import RecordingStream
+    labels, frames = synthetic.make_recording(hm_dict(), seed=11, n_frames=10)
+    sd = synthetic.make_state_dict(0)
+    poses = {}
+    for variant in ("persistent", "general", "general-no-graph"):
+        model = UmeTrackModel(sd).to("cuda")
+        tr = HandTracker(model, HandTrackerOpts())
+        tr.use_cuda_graphs = variant != "general-no-graph"
+        stream = RecordingStream(labels, frames)
+        out = []
+        for frame, gt in stream:
+            cc = tr.gen_crop_cameras([v.camera for v in frame.views], stream.camera_angles, stream.hand_model, gt, 1)
+            if variant != "persistent":
+                cc = {h: dict(v) for h, v in cc.items()}          # equal content, not the tracker's own object
+            res = tr.track_frame(frame, stream.hand_model, cc)
+            took_fast = tr._crop_cache is not None and tr._crop_cache["out"] is cc
+            assert took_fast == (variant == "persistent")
+            out.append({h: (p.joint_angles.copy(), p.wrist_xform.copy()) for h, p in res.hand_poses.items()})
+        poses[variant] = out
+    n_checked = 0
+    for a, b, c in zip(poses["persistent"], poses["general"], poses["general-no-graph"]):
+        assert a.keys() == b.keys() == c.keys()
+        for h in a:
+            for other in (b, c):
+                assert np.abs(a[h][0] - other[h][0]).max() < 2e-5            # joint angles (rad)
+                assert np.abs(a[h][1] - other[h][1]).max() < 2e-3            # wrist transform (mm)
+            n_checked += 1
+    assert n_checked >= 10
