@@ -251,3 +251,13 @@ def test_torch_idx_round_trip_fuzz(tmp_path):
     write_torch_idx_bin(p, recs)
     idx = TorchIdx(p)
     assert idx.is_msgpack and not idx.is_uniform and [idx.read_item(i) for i in range(3)] == recs
+
+
+def test_nvtx_ranges_are_off_by_default_and_cost_nothing():
+    from umetrack_b200 import nvtx
+    assert not nvtx.enabled()
+    with nvtx.stage("anything"):
+        pass
+    nvtx.push("anything")
+    nvtx.pop()
+    assert nvtx.stage("a") is nvtx.stage("b")          # the shared null context, no allocation per call

@@ -24,7 +24,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import numpy as np
 import torch
 
-from . import native
+from . import native, nvtx
 from .cameras import FISHEYE62_FIELDS
 from .hand_model import HandModel, load_hand_model_from_dict, scaled_hand_model
 from .ingest import FrameStager
@@ -158,6 +158,7 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
     lib = native.lib()
     R = len(recordings)
     hand_models = [load_hand_model_from_dict(lab["hand_model"]) for lab, _ in recordings]
+    nvtx.push("crop_cameras")
     # ---- 1. crop cameras of every recording (small device work + the host's item lists) ----------------
     plans, counts = [], []
     for (lab, frames), hm in zip(recordings, hand_models):
@@ -181,6 +182,8 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
         plans.append(plan)
         counts.append(cnt)
     base = np.cumsum([0] + [len(pl["t_i"]) for pl in plans])
+    nvtx.pop()
+    nvtx.push("resample")
     # ---- 2. resampling: frames go up in chunks through the staging ring (the upload of chunk k+1
     # overlaps the resampling of chunk k; the host only enqueues here, so uploads run back to back
     # across recordings); items are frame-major, so a chunk's items are contiguous ---------------------
@@ -199,6 +202,8 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
                     all_crops.data_ptr() + 4 * 9216 * (int(base[r]) + i0), 0, native.current_stream_ptr()),
                     "umt_resample_crops")
             stager.release(slot)
+    nvtx.pop()
+    nvtx.push("encoder")
     # ---- 3. backbone over every crop of every recording ---------------------------------------------
     feats = model.encode(all_crops) if len(all_crops) else torch.empty((0, 72, 6, 6), device=dev)
     with_items = [pl for pl in plans if len(pl["t_i"])]
@@ -209,6 +214,8 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
     for r in range(R):
         flat = counts[r].reshape(-1).astype(np.int64)
         start.append((int(base[r]) + np.concatenate([[0], np.cumsum(flat)[:-1]])).reshape(counts[r].shape))
+    nvtx.pop()
+    nvtx.push("time_scan")
     # ---- 4. time scan: hands of all recordings present at frame t form one batch ---------------------
     # All per-step descriptors are built on the host first (numpy), uploaded once, and the scan itself
     # is one C call per frame index with offset pointers (UmeTrackModel.tail_scan).
@@ -259,6 +266,8 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
         wr_all[slot] = wr
     out_ja = [ja_all[int(off[r]):int(off[r + 1])] for r in range(R)]
     out_wr = [wr_all[int(off[r]):int(off[r + 1])] for r in range(R)]
+    nvtx.pop()
+    nvtx.push("fk+metrics")
     # ---- 5. FK + metrics -----------------------------------------------------------------------------
     results = []
     for r, ((lab, _), hm) in enumerate(zip(recordings, hand_models)):
@@ -282,4 +291,5 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
         err = keypoint_errors_device(pred, gt)[v].cpu().numpy()      # hand-major, like (gt - tracked)[valid]
         results.append({"tracked_keypoints": tk, "gt_keypoints": gk, "valid_tracking": valid[r],
                         "per_frame_mean_error": err})
+    nvtx.pop()
     return results

@@ -166,7 +166,7 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
   cluster_sync_all();   // the peer's barriers exist before anything is signalled across the pair
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  if (threadIdx.x == 0) grid_launch_dependents();   // (after the TMEM allocation, see conv_umma_kernel)
+  grid_launch_dependents();   // (after the TMEM allocation, see conv_umma_kernel)
 
   if (warp == 0 && lane == 0) {
     // ===== A-patch producer (both CTAs): own 128 positions + halo, one 16-channel slice per stage =====

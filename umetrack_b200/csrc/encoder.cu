@@ -187,7 +187,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams P) {
   // The next layer may now set itself up and stream its weights while this one runs.  (Only after this
   // CTA owns its TMEM columns: a dependent CTA that took them first would wait for this grid while this
   // CTA waits for the columns.)
-  if (threadIdx.x == 0) grid_launch_dependents();
+  grid_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     // ===== A-patch producer: one 16-channel slice (2 planes hi [+2 planes lo]) per stage =====

@@ -17,7 +17,7 @@ from typing import Dict, List, NamedTuple, Optional, Tuple
 import numpy as np
 import torch
 
-from . import native
+from . import native, nvtx
 from .cameras import CameraModel, PinholePlaneCameraModel, resample_params
 from .crop_camera import gen_crop_parameters_from_points
 from .hand_model import HandModel, NUM_HANDS, NUM_JOINTS_PER_HAND, RIGHT_HAND_INDEX, scaled_hand_model
@@ -260,7 +260,8 @@ class HandTracker:
         if hands and self._device_crop_cameras and all(
                 type(c).__name__ == "Fisheye62CameraModel" and c.width == cameras[0].width
                 and c.height == cameras[0].height for c in cameras) and tuple(self._input_size) == (96, 96):
-            return self._gen_crop_cameras_device(cameras, camera_angles, hand_model, hands, min_num_crops)
+            with nvtx.stage("crop_cameras"):
+                return self._gen_crop_cameras_device(cameras, camera_angles, hand_model, hands, min_num_crops)
         out: Dict[int, Dict[int, PinholePlaneCameraModel]] = {}
         for hand_idx, pose in (gt_tracking or {}).items():
             if pose.hand_confidence < CONFIDENCE_THRESHOLD:
@@ -356,15 +357,18 @@ class HandTracker:
         if not crop_cameras:
             self.reset_history()
             return TrackingResult()
-        data, desc, skel = self._make_inputs(sample, hand_model, crop_cameras)
+        with nvtx.stage("inputs+resample"):
+            data, desc, skel = self._make_inputs(sample, hand_model, crop_cameras)
         # one CUDA-graph replay per frame; the graph's static outputs are read before returning
         m = self._model
         prev = getattr(m, "_frame_graphs", None)
         if prev is not None and self.use_cuda_graphs:
             m._frame_graphs = True
         try:
-            out = m.regress_pose_use_skeleton(data, desc, skel)
-            return self._gen_tracking_result(out, self._last_hands, crop_cameras)
+            with nvtx.stage("forward"):
+                out = m.regress_pose_use_skeleton(data, desc, skel)
+            with nvtx.stage("result"):
+                return self._gen_tracking_result(out, self._last_hands, crop_cameras)
         finally:
             if prev is not None:
                 m._frame_graphs = prev

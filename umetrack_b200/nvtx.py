@@ -1,0 +1,43 @@
+"""NVTX ranges around the stages of the path (crop cameras, resample, encoder, time scan, FK + metrics),
+for timelines taken with Nsight Systems.  Off unless UMETRACK_NVTX=1: a range is two calls into the
+NVTX library per stage, which the per-frame tracker (under 1 ms per frame) should not pay by default."""
+from __future__ import annotations
+
+import contextlib
+import os
+
+_ON = os.environ.get("UMETRACK_NVTX", "0") not in ("", "0")
+_NULL = contextlib.nullcontext()
+
+
+def enabled() -> bool:
+    return _ON
+
+
+def enable(on: bool = True) -> None:
+    global _ON
+    _ON = bool(on)
+
+
+def stage(name: str):
+    """Context manager: an NVTX range `umetrack/<name>` when enabled, else nothing."""
+    if not _ON:
+        return _NULL
+    import torch
+
+    return torch.cuda.nvtx.range("umetrack/" + name)
+
+
+def push(name: str) -> None:
+    """Open `umetrack/<name>` (for stages that are sections of a long function); close with pop()."""
+    if _ON:
+        import torch
+
+        torch.cuda.nvtx.range_push("umetrack/" + name)
+
+
+def pop() -> None:
+    if _ON:
+        import torch
+
+        torch.cuda.nvtx.range_pop()
