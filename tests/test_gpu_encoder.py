@@ -102,3 +102,36 @@ def test_halo_and_guard_rows_stay_zero_after_ragged_passes(setup):
     native.check(native.lib().umt_model_debug_halo_check(model._handle, ctypes.byref(bad), native.current_stream_ptr()),
                  "umt_model_debug_halo_check")
     assert bad.value == 0, f"{bad.value} halo / guard rows of the activation workspace are no longer zero"
+
+
+@pytest.mark.parametrize("mode", ["fp32", "fp16"])
+def test_small_batch_launch_variants_are_bit_identical(setup, monkeypatch, mode):
+    """A tracker frame (2-4 crops) runs the 128 / 256-channel layers as (tile, 64-channel slice) CTAs and
+    launches the convolutions as programmatic dependents.  Dependent launches change no arithmetic: bit-identical
+    features, pass after pass (an overlap bug would show up intermittently).  Slices change no arithmetic in the
+    16-bit modes either; in the split mode a 64-channel slice uses the merged form of the three products
+    (two accumulators added in the epilogue) where the whole layer uses one accumulator, i.e. the same products
+    summed in another order (and rounded to hi + lo again after each of the 14 layers): equal to ~1e-5."""
+    sd, _, imgs, _, _ = setup
+    model = UmeTrackModel(sd).to("cuda").set_mode(mode)
+    x = imgs[:4].cuda()
+    outs = {}
+    for name, slice_rows, overlap in (("default", None, None), ("no slices", "0", None), ("no overlap", None, "0"),
+                                      ("neither", "0", "0")):
+        for key, val in (("UMT_CONV_SLICE_ROWS", slice_rows), ("UMT_CONV_OVERLAP_MAX", overlap)):
+            if val is None:
+                monkeypatch.delenv(key, raising=False)
+            else:
+                monkeypatch.setenv(key, val)
+        a = model.encode(x).clone()
+        for _ in range(5):
+            assert torch.equal(model.encode(x), a), f"{name}: not reproducible"
+        outs[name] = a.cpu()
+    model.check_status()
+    assert torch.equal(outs["default"], outs["no overlap"]), f"dependent launches changed the result ({mode})"
+    assert torch.equal(outs["no slices"], outs["neither"]), f"dependent launches changed the result ({mode})"
+    if mode == "fp16":
+        assert torch.equal(outs["default"], outs["no slices"])
+    else:
+        scale = float(outs["default"].abs().max())
+        assert float((outs["default"] - outs["no slices"]).abs().max()) <= 5e-5 * scale   # (features vs oracle: 3e-4)
