@@ -5,9 +5,12 @@ and lib/tracker/tracking_result.py:14-30: tracker I/O is in millimetres, model I
 the model predicts left hands, right-hand crops are x-mirrored by the crop camera and the
 result un-mirrored; an empty `crop_cameras` resets the history and returns an empty result.
 
-What runs where: crop-camera selection (a few landmarks, float64) stays on the host; the
-landmark FK it needs, the crop resampling (`_warp_image`), the network and the result FK run
-in libumetrack_b200.so.
+What runs where: for the usual rig (FishEye62 views of one size) crop-camera generation runs on the
+device (`umt_crop_cameras`, float64) and only the chosen cameras' parameters come back to build the
+PinholePlaneCameraModel objects the API returns; any other camera model takes the host construction
+(`crop_camera.py`).  The landmark FK, the crop resampling (`_warp_image`), the network and the result
+FK run in libumetrack_b200.so.  A frame goes through persistent pinned / device buffers
+(`_FrameBuffers`): two uploads, two reads, one CUDA-graph replay, no allocation.
 """
 from __future__ import annotations
 
@@ -275,6 +278,12 @@ class HandTracker:
                 out[hand_idx] = per_hand
         return out
 
+    @staticmethod
+    def _crop_signature(crop_cameras) -> tuple:
+        """Hands, chosen cameras and the identity of the crop-camera objects: the persistent path is only
+        taken while the dict still holds exactly what gen_crop_cameras put there."""
+        return tuple((h, tuple((k, id(c)) for k, c in per.items())) for h, per in crop_cameras.items())
+
     def _buffers(self, n_cam: int, h: int, w: int) -> _FrameBuffers:
         n_pose = self._num_crop_points // 21
         if self._fb is None or self._fb.key != (n_cam, h, w, n_pose):
@@ -350,7 +359,7 @@ class HandTracker:
                 out[hand_idx] = per_hand
                 index[hand_idx] = i
         self._crop_cache = {"out": out, "index": index, "rows": rows, "views": [id(c) for c in cameras],
-                            "sig": tuple((h, tuple(v.keys())) for h, v in out.items())}
+                            "sig": self._crop_signature(out)}
         return out
 
     def track_frame(self, sample: InputFrame, hand_model: HandModel, crop_cameras) -> TrackingResult:
@@ -443,7 +452,7 @@ class HandTracker:
     def _make_inputs(self, sample: InputFrame, hand_model_mm: Optional[HandModel], crop_cameras):
         cache = self._crop_cache
         if (cache is not None and cache["out"] is crop_cameras and self._fb is not None
-                and cache["sig"] == tuple((h, tuple(v.keys())) for h, v in crop_cameras.items())
+                and cache["sig"] == self._crop_signature(crop_cameras)
                 and len(sample.views) == self._fb.key[0]
                 and all(isinstance(v.image, np.ndarray) and v.image.dtype == np.uint8 for v in sample.views)):
             return self._make_inputs_persistent(sample, hand_model_mm, crop_cameras, cache)
