@@ -1424,7 +1424,8 @@ void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode) {
   // it is not itself the bottleneck -- everywhere in the 3-product mode, and for Cout >= 64 in
   // the 16-bit modes.)  UMT_RES_MMA=0/1 forces one way.
   if (p.res_stages > 0) {
-    const int force = env_int("UMT_RES_MMA", -1);
+    int force = env_int("UMT_RES_MMA", -1);
+    force = env_int(("UMT_RES_MMA" + std::to_string(L.cout)).c_str(), force);   // per width: UMT_RES_MMA32=1 ...
     const bool epi = force >= 0 ? force == 0 : (split || L.cout >= 64);
     if (epi) { p.n_stages -= p.res_stages; p.res_epi = 1; }
   }
