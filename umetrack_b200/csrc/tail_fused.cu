@@ -4,11 +4,12 @@
 // (0.17 ms per step, 34 ms of host time per 256-step scan).  Here a sample's activations never leave
 // shared memory and the convolutions are plain float32 FMAs on the CUDA cores: two launches per step
 // (skeleton encoder + this kernel).
-//  * `tail_fused_kernel<1>`: one CTA per sample, weights read through L2 as they are used.  Measured on
-//    B200 (UMT_TAIL_DBG=1): 278 k cycles per sample, of which the four 3x3 regressor convolutions are 200 k
-//    (7.5 M FMAs): the inner loops wait for one L2 round trip per input channel, so a sample takes 0.16 ms
-//    whatever the batch, up to one CTA per SM -- on par with the 15-launch path in device time and 7x
-//    cheaper on the host.
+//  * `tail_fused_kernel<1>`: one CTA per sample.  Measured on B200 (UMT_TAIL_DBG=1): 239 k cycles per
+//    sample, of which the four 3x3 regressor convolutions (7.5 M FMAs) are 163 k with their weights staged
+//    through shared memory one chunk of 8 input channels ahead (read through L2 as they were needed they
+//    cost one round trip per input channel: 200 k) and the six 1x1 convolutions 57 k: 0.144 ms per step
+//    whatever the batch, up to one CTA per SM -- faster than the 15-launch path (0.17 ms) and 7x cheaper
+//    on the host.
 //  * `tail_fused_kernel<8>`, for up to 24 samples (a frame of the per-frame tracker, a frame index of a
 //    small time scan): a sample is spread over a CLUSTER of 8 CTAs.  Every CTA keeps the whole
 //    activation set in its own shared memory, computes one eighth of each layer's output channels from a
@@ -36,7 +37,10 @@ namespace umt {
 constexpr int kFusedThreads = 256;
 constexpr int kPad = 64;                       // a 6x6 map with a zero border: 8 x 8
 constexpr int kPoolFloats = 3 * 76 * kPad;     // three padded 76-channel maps; the 1x1 stages alias it
-constexpr int kFusedSmem = (kPoolFloats + 256) * 4;     // (the cluster variant adds two weight buffers, below)
+constexpr int kChunkCi = 8;                    // input channels per staged weight chunk of the one-CTA 3x3 convolution
+constexpr int kChunkFloats = kChunkCi * 9 * 76;
+constexpr int kFusedSmem = (kPoolFloats + 256 + 2 * kChunkFloats) * 4;   // pool, small arrays, two weight chunks
+constexpr int kClusterBase = (kPoolFloats + 256) * 4;                      // (the cluster variant adds two weight slices instead)
 
 // out[co][p] = act(bias[co] + sum_ci w[ci][co] * in[ci][p]) for the 36 pixels of a sample.
 // Work item = (output channel, half of the pixels); consecutive lanes = consecutive channels, so the
@@ -142,6 +146,85 @@ __device__ __forceinline__ void conv3x3_cta(const float* __restrict__ in, float*
   }
 }
 
+// The same convolution with the weights staged through shared memory: chunks of kChunkCi input channels
+// ([ci][tap][co], contiguous in global memory) arrive by cp.async one chunk ahead of the FMAs, so the loop
+// waits for no L2 round trip (conv3x3_cta above does, once per input channel: 50 k cycles per layer against
+// 33 k here).  Same work items, same FMA order per output element.  Called by all threads of the CTA.
+__device__ __forceinline__ void stage_chunk3x3(float* dst, const float* __restrict__ w, int c, int ci0) {
+  const int nci = (c - ci0 < kChunkCi) ? c - ci0 : kChunkCi;
+  const int n = nci * 9 * c;                         // 9 * c is a multiple of 4 for c = 72, 76
+  const float* src = w + (size_t)ci0 * 9 * c;
+  for (int i = 4 * (int)threadIdx.x; i < n; i += 4 * kFusedThreads) {
+    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst + i);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src + i) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void conv3x3_cta_staged(const float* __restrict__ in, float* __restrict__ out, int c,
+                                                   const float* __restrict__ w, const float* __restrict__ bias,
+                                                   const float* __restrict__ res, float* wbuf) {
+  const int item = threadIdx.x;
+  const bool active = item < 3 * c;
+  const int g = active ? item / c : 0, co = active ? item - g * c : 0;
+  float acc[2][6];
+  const float b = __ldg(bias + co);
+#pragma unroll
+  for (int y = 0; y < 2; ++y)
+#pragma unroll
+    for (int x = 0; x < 6; ++x) acc[y][x] = b;
+  const int n_chunks = (c + kChunkCi - 1) / kChunkCi;
+  stage_chunk3x3(wbuf, w, c, 0);
+  for (int ch = 0; ch < n_chunks; ++ch) {
+    if (ch + 1 < n_chunks) {
+      stage_chunk3x3(wbuf + ((ch + 1) & 1) * kChunkFloats, w, c, (ch + 1) * kChunkCi);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();                                   // chunk ch is in shared memory for every thread
+    if (active) {
+      const float* wb = wbuf + (ch & 1) * kChunkFloats + co;
+      const int ci0 = ch * kChunkCi, nci = (c - ci0 < kChunkCi) ? c - ci0 : kChunkCi;
+#pragma unroll 2
+      for (int cl = 0; cl < nci; ++cl) {
+        float wc[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) wc[k] = wb[(cl * 9 + k) * c];
+        float win[4][8];
+        const float4* src = reinterpret_cast<const float4*>(in + (ci0 + cl) * kPad + 2 * g * 8);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float4 lo = src[2 * r], hi = src[2 * r + 1];
+          win[r][0] = lo.x; win[r][1] = lo.y; win[r][2] = lo.z; win[r][3] = lo.w;
+          win[r][4] = hi.x; win[r][5] = hi.y; win[r][6] = hi.z; win[r][7] = hi.w;
+        }
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const float wv = wc[ky * 3 + kx];
+#pragma unroll
+            for (int y = 0; y < 2; ++y)
+#pragma unroll
+              for (int x = 0; x < 6; ++x) acc[y][x] = fmaf(wv, win[y + ky][x + kx], acc[y][x]);
+          }
+      }
+    }
+    __syncthreads();                                   // chunk ch's buffer may be refilled
+  }
+  if (active) {
+#pragma unroll
+    for (int y = 0; y < 2; ++y)
+#pragma unroll
+      for (int x = 0; x < 6; ++x) {
+        const int o = co * kPad + (2 * g + y + 1) * 8 + x + 1;
+        float v = acc[y][x];
+        if (res) v += res[o];
+        out[o] = fmaxf(v, 0.f);
+      }
+  }
+}
+
 // ---- cluster variant: helpers (kClusterCtas, cluster_slice_floats: model.cuh) ----
 
 __device__ __forceinline__ unsigned cluster_rank() {
@@ -188,7 +271,7 @@ __device__ __forceinline__ void pull_slices(float* buf, int cout, int stride, in
 // see no global-memory latency (the one-CTA variant is bound by exactly that: one L2 round trip per input
 // channel).
 constexpr int kWBufFloats = cluster_slice_floats(76 * 9);      // largest slice: a 3x3 layer of the k-head
-constexpr int kClusterSmem = kFusedSmem + 2 * kWBufFloats * 4;
+constexpr int kClusterSmem = kClusterBase + 2 * kWBufFloats * 4;
 struct Slice { int co0, nco, per; };
 template <int CS>
 __device__ __forceinline__ Slice slice_of(int cout, int rank) {
@@ -388,7 +471,7 @@ tail_fused_kernel(const FusedParams P) {
   auto c3 = [&](const float* in, float* out, const float* w, const float* bias, const float* res) {
     const float* wb = layer_begin(false);
     const long long t0 = P.dbg ? clock64() : 0;
-    if constexpr (CS == 1) conv3x3_cta(in, out, P.c, w, bias, res);
+    if constexpr (CS == 1) conv3x3_cta_staged(in, out, P.c, w, bias, res, wbuf);
     else conv3x3_cl(in, out, P.c, slice_of<CS>(P.c, rank), wb, res);
     if (P.dbg) dbg_c3 += clock64() - t0;
     layer_end(out, P.c, kPad);
