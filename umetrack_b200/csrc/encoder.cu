@@ -459,8 +459,10 @@ static size_t conv_smem_bytes(const ConvParams& p, int cout, bool split) {
 }
 
 constexpr int kMaxDevices = 64;
+static int env_int(const char* name, int dflt);
 static long long* g_conv_dbg = nullptr;   // set by umt_debug_set_conv_timeline (tools only)
-void set_conv_debug_buffer(long long* p) { g_conv_dbg = p; }
+static int g_conv_dbg_launch = 0;         // UMT_CONV_DBG_STRIDE=n: launch i writes its counters at buffer + i * n
+void set_conv_debug_buffer(long long* p) { g_conv_dbg = p; g_conv_dbg_launch = 0; }
 
 static int sm_count() {
   static int n = 0;
@@ -485,6 +487,10 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
   }
   ConvParams pd = p;
   pd.dbg = g_conv_dbg;
+  if (g_conv_dbg) {
+    const int stride = env_int("UMT_CONV_DBG_STRIDE", 0);
+    if (stride > 0) pd.dbg = g_conv_dbg + (size_t)(g_conv_dbg_launch++) * stride;
+  }
   {  // the opt-in shared-memory size is a per-device attribute of each kernel: set it once (and when it grows)
     static size_t have[3][kMaxDevices] = {};
     const int epi = p.dense_out ? kEpiDense : p.res_epi ? kEpiResidual : kEpiPlain;
