@@ -57,6 +57,7 @@ struct alignas(64) PairParams {
   int n_stages;
   int relu, res_epi, phase_out;
   int overlap_launch;       // host only: launch with programmatic stream serialization
+  long long* dbg;           // optional [pairs][16] cycle counters, slots as in conv_umma_kernel (tools only)
   uint8_t st_src[kPairMaxStages], st_chunk[kPairMaxStages], st_ntaps[kPairMaxStages];
   short tap_shift[kMaxTaps];
   uint8_t st_tap0[kPairMaxStages];
@@ -229,22 +230,32 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
     const uint32_t a_hi32 = (uint32_t)(a_desc_base >> 32), b_hi32 = (uint32_t)(b_desc_base >> 32);
     const uint32_t a_lo_plane16 = (2u * a_plane_bytes) >> 4;
     int it = 0, kb = 0, tc = 0;
+    long long w_acc = 0, w_a = 0, w_b = 0;
+    const long long t_begin = clock64();
+    unsigned long long g_begin = 0;
+    if (P.dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_begin));
     for (int tile = pair_id; tile < P.n_tiles; tile += n_pairs, ++tc) {
       const int buf = tc % n_buf;
+      const long long c_acc = P.dbg ? clock64() : 0;
       mbar_wait(acc_empty(buf), ((uint32_t)(tc / n_buf) & 1u) ^ 1u);   // both CTAs' epilogues drained this buffer
+      if (P.dbg) w_acc += clock64() - c_acc;
       tc_fence_after();
       const uint32_t d0 = tmem_base + (uint32_t)buf * buf_cols;
       uint32_t any = 0;
       for (int i = 0; i < P.n_stages; ++i, ++it) {
         const int aslot = it % n_a;
+        const long long c_a = P.dbg ? clock64() : 0;
         mbar_wait(a_full(aslot), (uint32_t)(it / n_a) & 1u);
+        if (P.dbg) w_a += clock64() - c_a;
         const uint32_t a_s = smem_u32(a_base + (size_t)aslot * a_stage_stride);
         const uint32_t a_lo32 = (uint32_t)(a_desc_base & 0xFFFFFFFFu) | ((a_s >> 4) & 0x3FFFu);
         const int nt = P.st_ntaps[i], tap0 = P.st_tap0[i];
         for (int t0 = 0; t0 < nt; t0 += G, ++kb) {
           const int n = min(G, nt - t0);
           const int bslot = kb % n_b;
+          const long long c_b = P.dbg ? clock64() : 0;
           mbar_wait(b_full(bslot), (uint32_t)(kb / n_b) & 1u);
+          if (P.dbg) w_b += clock64() - c_b;
           tc_fence_after();
           const uint32_t b_s0 = smem_u32(b_base + (size_t)bslot * b_stage_bytes);
           const uint32_t b_lo32 = (uint32_t)(b_desc_base & 0xFFFFFFFFu) | ((b_s0 >> 4) & 0x3FFFu);
@@ -287,12 +298,23 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
       if (leader) tc_commit_pair(acc_full(buf));
       __syncwarp();
     }
+    if (P.dbg && leader) {
+      long long* o = P.dbg + pair_id * 16;
+      o[3] = w_acc; o[4] = w_a; o[5] = w_b; o[6] = clock64() - t_begin; o[7] = tc;
+      unsigned long long g_end;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_end));
+      unsigned smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      o[10] = (long long)g_begin; o[11] = (long long)g_end; o[12] = smid;
+    }
   } else if (warp >= 4) {
     // ===== epilogue (both CTAs): own 128 rows of the accumulator -> bias / residual / ReLU -> global =====
     grid_dependency_wait();     // residual rows and the output tensor belong to earlier launches until they are done
     const int lgrp = warp & 3;
     int tc = 0;
     bool fp16_over = false;
+    long long w_full = 0;
+    const long long e_begin = clock64();
     constexpr int kStep = MERGE ? 16 : 32, kRows = kStep / 8;
     for (int tile = pair_id; tile < P.n_tiles; tile += n_pairs, ++tc) {
       const int buf = tc % n_buf;
@@ -322,7 +344,9 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
         }
       }
       if (sb == 0) {
+        const long long c_f = P.dbg ? clock64() : 0;
         mbar_wait(acc_full(buf), (uint32_t)(tc / n_buf) & 1u);
+        if (P.dbg) w_full += clock64() - c_f;
         tc_fence_after();
       }
       const FlatTensor& T = P.out[o.tensor];
@@ -378,6 +402,10 @@ conv_pair_kernel(const __grid_constant__ PairParams P) {
     }
     if (MODE == UMT_MODE_FP16 && P.status && __any_sync(0xFFFFFFFFu, fp16_over) && lane == 0)
       atomicOr(P.status, (unsigned)UMT_STATUS_FP16_RANGE);
+    if (P.dbg && leader_cta && warp == 4 && lane == 0) {
+      P.dbg[pair_id * 16 + 8] = w_full;
+      P.dbg[pair_id * 16 + 9] = clock64() - e_begin;
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -553,6 +581,7 @@ int launch_conv_pair(const ConvParams& c, int cout, int mode, cudaStream_t st) {
   p.patch_rows = p.n_box * p.box_rows;
   p.relu = c.relu; p.res_epi = c.res_epi; p.phase_out = c.phase_out;
   p.overlap_launch = c.overlap_launch;
+  p.dbg = next_conv_debug_slot();
   p.bias = c.bias;
   p.status = c.status;
   p.res = c.res;

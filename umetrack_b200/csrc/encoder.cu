@@ -463,6 +463,12 @@ static int env_int(const char* name, int dflt);
 static long long* g_conv_dbg = nullptr;   // set by umt_debug_set_conv_timeline (tools only)
 static int g_conv_dbg_launch = 0;         // UMT_CONV_DBG_STRIDE=n: launch i writes its counters at buffer + i * n
 void set_conv_debug_buffer(long long* p) { g_conv_dbg = p; g_conv_dbg_launch = 0; }
+// counters of the next launch (nullptr in production); conv_pair.cu asks here
+long long* next_conv_debug_slot() {
+  if (!g_conv_dbg) return nullptr;
+  const int stride = env_int("UMT_CONV_DBG_STRIDE", 0);
+  return stride > 0 ? g_conv_dbg + (size_t)(g_conv_dbg_launch++) * stride : g_conv_dbg;
+}
 
 static int sm_count() {
   static int n = 0;
@@ -486,11 +492,7 @@ static int launch_conv_t(const ConvParams& p, cudaStream_t st) {
     kernel = conv_umma_kernel<COUT, MODE, kEpiResidual>;
   }
   ConvParams pd = p;
-  pd.dbg = g_conv_dbg;
-  if (g_conv_dbg) {
-    const int stride = env_int("UMT_CONV_DBG_STRIDE", 0);
-    if (stride > 0) pd.dbg = g_conv_dbg + (size_t)(g_conv_dbg_launch++) * stride;
-  }
+  pd.dbg = next_conv_debug_slot();
   {  // the opt-in shared-memory size is a per-device attribute of each kernel: set it once (and when it grows)
     static size_t have[3][kMaxDevices] = {};
     const int epi = p.dense_out ? kEpiDense : p.res_epi ? kEpiResidual : kEpiPlain;

@@ -162,6 +162,7 @@ int encoder_halo_check(umt_model* m, long long* host_nonzero, cudaStream_t st);
 size_t encoder_workspace_bytes(int chunk_images);
 void encoder_bind(umt_model* m, uint8_t* base);
 void set_conv_debug_buffer(long long* p);
+long long* next_conv_debug_slot();
 int build_conv(umt_model* m, ConvLayer& L, const Folded& main, const Folded* ds);
 int launch_conv(const ConvParams& p, int cout, int mode, cudaStream_t st);
 void finalize_conv_params(ConvParams& p, const ConvLayer& L, int mode);
