@@ -220,38 +220,37 @@ def track_recordings_batched(model, recordings: Sequence[Tuple[dict, np.ndarray]
     # All per-step descriptors are built on the host first (numpy), uploaded once, and the scan itself
     # is one C call per frame index with offset pointers (UmeTrackModel.tail_scan).
     T_max = max(c.shape[0] for c in counts)
-    history = np.zeros((R, 2), dtype=bool)
     off = np.cumsum([0] + [2 * c.shape[0] for c in counts])      # output slot of (r, h, t): off[r] + h*T_r + t
-    valid = [np.zeros((2, c.shape[0]), dtype=bool) for c in counts]
-    rows_sr, rows_mem, rows_use, rows_hand, rows_rec, rows_slot, step_rows = [], [], [], [], [], [], []
-    for t in range(T_max):
-        first = len(rows_mem)
-        for r in range(R):
-            if t >= counts[r].shape[0]:
-                continue
-            present = [h for h in range(2) if counts[r][t, h] > 0]
-            if not present:
-                history[r, :] = False            # frame without hands: reset_history (tracker.py:147-150)
-                continue
-            for h in present:
-                s0 = int(start[r][t, h])
-                rows_sr.append((s0, s0 + int(counts[r][t, h])))
-                rows_mem.append(r * 2 + h)
-                rows_use.append(bool(history[r, h]))
-                rows_hand.append(h)
-                rows_rec.append(r)
-                rows_slot.append(int(off[r]) + h * counts[r].shape[0] + t)
-                valid[r][h, t] = True
-            for h in range(2):
-                history[r, h] = h in present     # tracker.py:278-285
-        step_rows.append((first, len(rows_mem) - first))
+    valid = [(c > 0).T.copy() for c in counts]                   # [2, T_r]
+    # One row per (frame, recording, hand) with crops, ordered by frame index, then recording, then hand.
+    # A hand uses its memory iff it was tracked in the previous frame: after a frame the history is "hand in
+    # present" (tracker.py:278-285), and a frame without hands clears it (tracker.py:147-150) -- both are
+    # `present[t - 1, h]`.  (numpy instead of a Python loop over T x R: 25 ms per 32 x 256 frames.)
+    parts = []
+    for r in range(R):
+        c = counts[r].astype(np.int64)
+        T_r = c.shape[0]
+        pres = c > 0
+        prev = np.zeros_like(pres)
+        prev[1:] = pres[:-1]
+        t_i, h_i = np.nonzero(pres)
+        s0 = start[r][t_i, h_i].astype(np.int64)
+        parts.append(np.stack([t_i, np.full_like(t_i, r), h_i, s0, s0 + c[t_i, h_i], prev[t_i, h_i].astype(np.int64),
+                               int(off[r]) + h_i * T_r + t_i], axis=1))
+    rows = np.concatenate(parts).astype(np.int64) if parts else np.zeros((0, 7), dtype=np.int64)
+    rows = rows[np.lexsort((rows[:, 2], rows[:, 1], rows[:, 0]))]
+    per_t = np.bincount(rows[:, 0], minlength=T_max)
+    first_t = np.concatenate([[0], np.cumsum(per_t)[:-1]])
+    step_rows = list(zip(first_t.tolist(), per_t.tolist()))
+    rows_sr, rows_mem, rows_use = rows[:, 3:5], rows[:, 1] * 2 + rows[:, 2], rows[:, 5].astype(np.bool_)
+    rows_hand, rows_rec, rows_slot = rows[:, 2], rows[:, 1], rows[:, 6]
     ja_all = torch.zeros((int(off[-1]), 22), dtype=torch.float32, device=dev)
     wr_all = torch.eye(4, device=dev).repeat(int(off[-1]), 1, 1)
-    if rows_mem:
+    if len(rows_mem):
         skel_axes = torch.stack([hm.joint_rotation_axes.float() for hm in hand_models]).to(dev)
         skel_rest = torch.stack([scaled_hand_model(hm, MM_TO_M).joint_rest_positions.float() for hm in hand_models]).to(dev)
         def dev_array(rows, dtype):      # numpy first: torch.tensor on a long Python list is ~10x slower
-            return torch.from_numpy(np.asarray(rows, dtype=dtype)).to(dev)
+            return torch.from_numpy(np.ascontiguousarray(rows, dtype=dtype)).to(dev)
 
         ridx = dev_array(rows_rec, np.int64)
         ja, wr, _ = model.tail_scan(

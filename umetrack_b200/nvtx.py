@@ -28,12 +28,26 @@ def stage(name: str):
     return torch.cuda.nvtx.range("umetrack/" + name)
 
 
+# UMETRACK_STAGE_TIMES=1 (tools/profile_batched.py): push / pop also synchronise the device and add the
+# stage's wall time to `stage_times` -- a serialised breakdown, not a measurement of the pipelined run.
+_TIMES = os.environ.get("UMETRACK_STAGE_TIMES", "0") not in ("", "0")
+stage_times: dict = {}
+_open: list = []
+
+
 def push(name: str) -> None:
     """Open `umetrack/<name>` (for stages that are sections of a long function); close with pop()."""
     if _ON:
         import torch
 
         torch.cuda.nvtx.range_push("umetrack/" + name)
+    if _TIMES:
+        import time
+
+        import torch
+
+        torch.cuda.synchronize()
+        _open.append((name, time.perf_counter()))
 
 
 def pop() -> None:
@@ -41,3 +55,11 @@ def pop() -> None:
         import torch
 
         torch.cuda.nvtx.range_pop()
+    if _TIMES and _open:
+        import time
+
+        import torch
+
+        torch.cuda.synchronize()
+        name, t0 = _open.pop()
+        stage_times[name] = stage_times.get(name, 0.0) + time.perf_counter() - t0
